@@ -1,0 +1,157 @@
+"""Pins the CPU oracle (oracle/mdd_oracle.c) against outputs of the REAL reference recorded in tests/golden/
+(written by oracle/gen_golden.py in the build container) and against torch CPU ctc_loss.  CPU-only."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import jload, npz
+from oracle import api as O
+
+
+CTC_CASES = ["basic", "repeat_ragged", "one_d", "infeasible", "infeasible_zi", "c42", "tiny"]
+
+
+@pytest.mark.parametrize("name", CTC_CASES)
+def test_ctc_oracle_vs_torch_golden(name):
+    z = npz("ctc_small.npz")
+    g = lambda k: z[name + "/" + k]
+    zi = bool(g("zero_inf"))
+    r = O.ctc_loss(g("lp"), g("targets"), g("in_len"), g("tgt_len"), zero_infinity=zi, want_alpha=True)
+    np.testing.assert_allclose(r["nll"], g("nll_f64"), rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(r["grad"], g("grad_f64"), rtol=0, atol=1e-12, equal_nan=True)
+    a, ga = r["alpha"], g("alpha_f64")
+    S = a.shape[2]
+    assert np.array_equal(np.isneginf(a), np.isneginf(ga[:, :, :S]))
+    fin = np.isfinite(a)
+    np.testing.assert_allclose(a[fin], ga[:, :, :S][fin], rtol=0, atol=1e-11)
+    r32 = O.ctc_loss(g("lp"), g("targets"), g("in_len"), g("tgt_len"), zero_infinity=zi, dtype=np.float32)
+    np.testing.assert_allclose(r32["nll"], g("nll_f32"), rtol=1e-5)
+    np.testing.assert_allclose(r32["grad"], g("grad_f32"), rtol=0, atol=2e-5, equal_nan=True)   # fp32 vs fp32 rounding
+
+
+def test_ctc_oracle_vs_torch_live():
+    g = torch.Generator().manual_seed(3)
+    T, B, C, L = 40, 6, 11, 8
+    lp = torch.log_softmax(torch.randn(T, B, C, generator=g), -1).double().requires_grad_(True)
+    tg = torch.randint(1, C, (B, L), generator=g)
+    il = torch.tensor([40, 40, 31, 22, 40, 17])
+    tl = torch.tensor([8, 3, 8, 5, 0, 8])
+    go = torch.rand(B, generator=g).double()
+    nll = torch.nn.functional.ctc_loss(lp, tg, il, tl, reduction="none")
+    (nll * go).sum().backward()
+    r = O.ctc_loss(lp.detach().numpy(), tg.numpy(), il.numpy(), tl.numpy(), grad_out=go.numpy())
+    np.testing.assert_allclose(r["nll"], nll.detach().numpy(), rtol=1e-12)
+    np.testing.assert_allclose(r["grad"], lp.grad.numpy(), atol=1e-12)
+
+
+def test_greedy_oracle_vs_reference():
+    z, js = npz("greedy.npz"), jload("greedy.json.gz")
+    for i, case in js.items():
+        voc = {int(k): v for k, v in case["vocab"].items()}
+        got = O.greedy_decode(z[i + "/lp"], z[i + "/lens"], voc)
+        assert got == case["out"], i
+
+
+def test_beam_oracle_vs_reference_small(arpa):
+    z, meta = npz("beam_small.npz"), jload("beam_small.json.gz")
+    n_exc = 0
+    for i, m in enumerate(meta):
+        voc = {k: w for k, w in enumerate(m["vocab"])}
+        lm = O.lm_table(arpa, voc, m["C"])
+        probs = z[str(i)][None]
+        toks, olen, st, _ = O.beam_tokens(probs, [m["len"]], m["W"], 0, lm, m["alpha"])
+        if isinstance(m["out"], dict):
+            n_exc += 1
+            assert O.BEAM_EXC[int(st[0])].__name__ == m["out"]["exc"], (i, st, m["out"])
+        else:
+            assert st[0] == 0, (i, st, m["out"])
+            assert " ".join(voc[int(k)] for k in toks[0, :olen[0]]) == m["out"], i
+    assert n_exc >= 5      # the fixture exercises the reference's crash modes
+
+
+def test_beam_oracle_vs_reference_c4(arpa, vocab43):
+    z, meta = npz("beam_c4.npz"), jload("beam_c4.json.gz")
+    lm = O.lm_table(arpa, vocab43, 43)
+    for alpha in (0.0, 0.3):
+        want = meta["out_alpha_%g" % alpha]
+        toks, olen, st, _ = O.beam_tokens(z["probs"], meta["lens"], 10, 0, lm, alpha)
+        for b, w in enumerate(want):
+            if isinstance(w, dict):
+                assert O.BEAM_EXC[int(st[b])].__name__ == w["exc"]
+            else:
+                assert st[b] == 0 and " ".join(vocab43[int(k)] for k in toks[b, :olen[b]]) == w, (alpha, b)
+
+
+def test_lm_table_vs_reference(arpa, vocab43):
+    want = npz("lm_table.npz")["table"]
+    got = O.lm_table(arpa, vocab43, 43)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    assert np.array_equal(got[~np.isnan(got)], want[~np.isnan(want)])       # bit-exact fp64
+
+
+def test_wer_corpus_totals():
+    """4976 / 7923 / 4423 / 7934 over 29087 reference phones; per-pair paths for one corpus."""
+    data = jload("wer_corpus.json.gz")
+    for name, c in data.items():
+        words = {}
+        hyp = [[words.setdefault(w, len(words)) for w in h.split()] for h in c["hyp"]]
+        ref = [[words.setdefault(w, len(words)) for w in r.split()] for r in c["ref"]]
+        dist, paths, st = O.edit_align(hyp, ref)
+        assert not st.any()
+        assert int(dist.sum()) == c["total"], name
+        assert c["ref_tokens"] == 29087
+        assert dist.tolist() == c["dist"]
+        if c["paths"]:
+            assert ["".join(p) for p in paths] == c["paths"]
+
+
+def _mdd_from_strings(decoded, canonical):
+    hyp = [w for w in decoded.split(" ") if w != "sil"]
+    ref = [w for w in canonical.split(" ") if w != "sil"]
+    dn = " ".join(hyp).replace("err", "").replace("  ", " ")
+    cn = " ".join(ref)
+    words = {}
+    d = [words.setdefault(w, len(words)) for w in dn.split()]
+    c = [words.setdefault(w, len(words)) for w in cn.split()]
+    inv = {v: k for k, v in words.items()}
+    inv[O.PAD_D], inv[O.PAD_I] = "D", "I"
+    dist, paths, st = O.edit_align([d], [c])
+    if st[0]:
+        return {"exc": "TypeError"}
+    r = O.mdd_post(d, c, paths[0])
+    return {"path0": paths[0], "dec": [inv[k] for k in r["dec"]], "can": [inv[k] for k in r["can"]], "path": r["ops"],
+            "ins": [inv[k] for k in r["ins"]], "sub": [inv[k] for k in r["sub"]], "del": [inv[k] for k in r["del"]],
+            "correct": r["correct"], "del_sub": r["del_sub"],
+            "score": O.mdd_score(len(r["ins"]), r["correct"], r["del_sub"])}
+
+
+def test_mdd_post_oracle_vs_reference():
+    cases = jload("mdd_post.json.gz")
+    n_exc = 0
+    for i, c in enumerate(cases):
+        got = _mdd_from_strings(c["decoded"], c["canonical"])
+        want = dict(c["out"])
+        want.pop("printed", None)
+        n_exc += "exc" in want
+        assert got == want, (i, c["decoded"], c["canonical"])
+    assert n_exc >= 1
+
+
+def test_prefix_score_invariants():
+    """psi(l.eos) == -nll (torch fp64) and P(g...) = P(g ends) + sum_c P(g.c ...)."""
+    g = torch.Generator().manual_seed(9)
+    T, C = 30, 6
+    x = torch.log_softmax(torch.randn(T, C, generator=g).double(), -1)
+    for labels in ([1, 2, 3], [2, 2, 4], [5], [1, 1, 1, 2, 2]):
+        r = O.prefix_init(x.numpy())
+        last, psi_g = -1, 0.0
+        for n, c in enumerate(labels):
+            psi, rr, eos = O.prefix_score(x.numpy(), r, last, n)
+            if n > 0:
+                tot = np.logaddexp.reduce(np.append(psi[1:], eos))
+                assert abs(tot - psi_g) < 1e-10
+            psi_g, r, last = psi[c], rr[c], c
+        _, _, eos = O.prefix_score(x.numpy(), r, last, len(labels))
+        nll = torch.nn.functional.ctc_loss(x[:, None, :], torch.tensor([labels]), torch.tensor([T]),
+                                           torch.tensor([len(labels)]), reduction="none")
+        assert abs(eos + float(nll)) < 1e-10
