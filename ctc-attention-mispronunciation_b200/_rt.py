@@ -1,0 +1,35 @@
+"""Small runtime helpers shared by the host-side drop-ins: device selection, workspace cache, stream handle."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+_ws_cache = {}
+
+
+def device(t=None) -> torch.device:
+    """The CUDA device the call runs on.  Raises (no CPU fallback) when CUDA is unavailable."""
+    if t is not None and isinstance(t, torch.Tensor) and t.is_cuda:
+        return t.device
+    if not torch.cuda.is_available():
+        raise _lib.MddCtcLibraryError("mddctc needs a CUDA device (sm_100a); there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def workspace(nbytes: int, dev: torch.device, tag: str = "ws") -> torch.Tensor:
+    """Grow-only per-(device, tag) scratch buffer; the C ABI never allocates."""
+    key = (dev.index, tag)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+        _ws_cache[key] = buf
+    return buf
+
+
+def stream_ptr(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def ptr(t) -> int:
+    return 0 if t is None else t.data_ptr()

@@ -1,0 +1,108 @@
+// capi.cu -- C ABI entry points for the CTC loss (include/mddctc.h) + library bookkeeping.
+#include "common.cuh"
+#include "ctc_params.cuh"
+
+namespace mdd {
+int64_t g_launch_count = 0;
+}
+using namespace mdd;
+
+extern "C" int mdd_version(void) { return 100; }
+
+extern "C" const char* mdd_error_string(int code) {
+    switch (code) {
+        case MDD_OK: return "ok";
+        case MDD_E_ARG: return "invalid argument";
+        case MDD_E_WORKSPACE: return "workspace too small";
+        case MDD_E_CUDA: return "CUDA runtime error (no device, or launch failure)";
+        case MDD_E_UNSUPPORTED: return "shape not supported by this build";
+        default: return "unknown error";
+    }
+}
+
+extern "C" int64_t mdd_launch_count(void) { return g_launch_count; }
+extern "C" void mdd_launch_count_reset(void) { g_launch_count = 0; }
+
+namespace {
+struct CtcWs {
+    size_t off_offsets, off_flags, off_ckpt, off_fast, total;
+};
+CtcWs ctc_ws_layout(int T, int B, int C, int Lmax, int algo) {
+    CtcWs w{};
+    size_t o = 0;
+    w.off_offsets = o; o = align_up(o + (size_t)B * 8, 256);
+    w.off_flags = o;   o = align_up(o + (size_t)B * 4, 256);
+    w.off_ckpt = o;
+    const bool fast = algo != 1 && ctc_fast_supported(C, Lmax);
+    if (algo == 1 || !fast || algo == 0) o = align_up(o + ctc_log_ckpt_bytes(T, B, Lmax), 256);
+    w.off_fast = o;
+    if (fast) o = align_up(o + ctc_fast_ws_bytes(T, B, Lmax), 256);
+    w.total = o;
+    return w;
+}
+}  // namespace
+
+extern "C" int mdd_ctc_loss_workspace_bytes(int T, int B, int C, int max_target_len, int algo, size_t* bytes) {
+    if (!bytes || T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || algo < 0 || algo > 2)
+        return MDD_E_ARG;
+    *bytes = ctc_ws_layout(T, B, C, max_target_len, algo).total;
+    return MDD_OK;
+}
+
+extern "C" int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t stride_t, int64_t stride_b,
+                            const int64_t* targets, int64_t tgt_stride, const int64_t* input_lengths,
+                            const int64_t* target_lengths, int max_target_len, int blank, int zero_infinity,
+                            const float* grad_out, float grad_out_scalar, float* nll, float* grad, float* loss_sum,
+                            int32_t* status, int algo, void* workspace, size_t workspace_bytes, mdd_stream_t stream) {
+    if (T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || blank < 0 || blank >= C || algo < 0 ||
+        algo > 2)
+        return MDD_E_ARG;
+    if (B == 0) return MDD_OK;
+    if ((!log_probs && T > 0) || !input_lengths || !target_lengths || !nll || (!targets && max_target_len > 0))
+        return MDD_E_ARG;
+    if (max_target_len > 2047) return MDD_E_UNSUPPORTED;
+    const CtcWs w = ctc_ws_layout(T, B, C, max_target_len, algo);
+    if (!workspace || workspace_bytes < w.total) return MDD_E_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* ws = (unsigned char*)workspace;
+
+    CtcParams p{};
+    p.lp = log_probs; p.T = T; p.B = B; p.C = C; p.stride_t = stride_t; p.stride_b = stride_b;
+    p.targets = targets; p.tgt_stride = tgt_stride; p.in_len = input_lengths; p.tgt_len = target_lengths;
+    p.Lmax = max_target_len; p.blank = blank; p.zero_inf = zero_infinity;
+    p.grad_out = grad_out; p.gscalar = grad_out_scalar; p.nll = nll; p.grad = grad; p.status = status;
+    p.tgt_offsets = reinterpret_cast<const int64_t*>(ws + w.off_offsets);
+    p.flags = reinterpret_cast<int32_t*>(ws + w.off_flags);
+    p.ckpt = reinterpret_cast<float*>(ws + w.off_ckpt);
+    int rc;
+    if (tgt_stride == 0) {
+        rc = launch_tgt_offsets(target_lengths, B, reinterpret_cast<int64_t*>(ws + w.off_offsets), st);
+        if (rc) return rc;
+    }
+    const bool fast = algo != 1 && ctc_fast_supported(C, max_target_len) && T > 0;
+    if (algo == 2 && !fast) return MDD_E_UNSUPPORTED;
+    if (fast) {
+        rc = launch_ctc_fast(p, ws + w.off_fast, st);           // flags[b] != 0 -> utterance needs the log-space path
+        if (rc) return rc;
+        if (algo == 0) {
+            p.only_flagged = 1;
+            rc = launch_ctc_log(p, st);
+            if (rc) return rc;
+        }
+    } else {
+        p.only_flagged = 0;
+        rc = launch_ctc_log(p, st);
+        if (rc) return rc;
+    }
+    if (loss_sum) {
+        rc = launch_sum_nll(nll, B, loss_sum, st);
+        if (rc) return rc;
+    }
+    return MDD_OK;
+}
+
+extern "C" int mdd_ctc_scale_grad(float* grad, int T, int B, int C, const float* scale, float scalar,
+                                  mdd_stream_t stream) {
+    if (!grad || T < 0 || B < 0 || C <= 0) return MDD_E_ARG;
+    return launch_scale_grad(grad, T, B, C, scale, scalar, (cudaStream_t)stream);
+}

@@ -1,0 +1,46 @@
+// ctc_params.cuh -- launch parameters shared by the CTC loss kernels
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mdd {
+
+struct CtcParams {
+    const float* lp;          // (T,B,C), strides (stride_t, stride_b, 1)
+    int T, B, C;
+    int64_t stride_t, stride_b;
+    const int64_t* targets;
+    int64_t tgt_stride;       // 0 -> concatenated, use tgt_offsets
+    const int64_t* tgt_offsets;
+    const int64_t* in_len;
+    const int64_t* tgt_len;
+    int Lmax;
+    int blank;
+    int zero_inf;
+    const float* grad_out;    // [B] or null
+    float gscalar;
+    float* nll;               // [B]
+    float* grad;              // (T,B,C) contiguous or null
+    int32_t* status;          // [B] or null
+    // log-space kernel
+    float* ckpt;              // [B][n_ckpt][2*Lmax+1]
+    int K, n_ckpt;
+    int only_flagged;         // process only utterances with flags[b] != 0
+    int32_t* flags;           // [B] fast path -> fallback requests
+};
+
+int ctc_log_chunk(int Lmax);
+size_t ctc_log_ckpt_bytes(int T, int B, int Lmax);
+int launch_tgt_offsets(const int64_t* tgt_len, int B, int64_t* off, cudaStream_t st);
+int launch_ctc_log(CtcParams p, cudaStream_t st);
+
+// rescaled linear-domain fast path (ctc_fast.cu)
+bool ctc_fast_supported(int C, int Lmax);
+size_t ctc_fast_ws_bytes(int T, int B, int Lmax);
+int launch_ctc_fast(CtcParams p, void* ws, cudaStream_t st);
+
+// deterministic sum of nll[B] -> loss_sum (reduce.cu)
+int launch_sum_nll(const float* nll, int B, float* out, cudaStream_t st);
+int launch_scale_grad(float* grad, int T, int B, int C, const float* scale, float scalar, cudaStream_t st);
+
+}  // namespace mdd

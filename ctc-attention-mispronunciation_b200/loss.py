@@ -1,0 +1,163 @@
+"""nn.CTCLoss-compatible module on the sm_100a kernels.
+
+Drop-in for the call sites egs/attention_aug/steps/train_ctc.py:186,72,96 and egs/cnn-rnn-ctc/steps/train_ctc.py:148,51,67:
+
+    loss_fn = CTCLoss(reduction='sum')
+    loss = loss_fn(out, targets, input_sizes, target_sizes); loss /= batch_size; loss.backward()
+
+Semantics follow torch.nn.functional.ctc_loss: blank/reduction/zero_infinity, (T,B,C) or
+(T,C) log-probs, 2-D padded or 1-D concatenated targets, lengths as tensors (any device) or sequences, 'mean' dividing
+by clamp_min(target_length, 1), inf loss / NaN gradient for infeasible alignments unless zero_infinity.
+
+The gradient is produced in the same launch as the loss (one pass over the log-probs); autograd's backward only scales
+it by the upstream gradient.  Compute dtype is fp32 (fp64 inputs are accepted and computed in fp32).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib, _rt
+
+
+def _as_len_tensor(x, dev):
+    if isinstance(x, torch.Tensor):
+        return x.to(device=dev, dtype=torch.int64).contiguous(), (x if not x.is_cuda else None)
+    t = torch.as_tensor(list(x), dtype=torch.int64)
+    return t.to(dev), t
+
+
+def ctc_loss_raw(log_probs, targets, input_lengths, target_lengths, blank=0, zero_infinity=False, want_grad=True,
+                 grad_out=None, grad_scalar=1.0, algo=0, validate=True, loss_sum=None, nll=None, grad=None,
+                 status=None):
+    """One call into mdd_ctc_loss.  Returns (nll[B], grad[T,B,C] or None, status[B]); everything stays on the device."""
+    L = _lib.lib()
+    if log_probs.dim() == 2:
+        log_probs = log_probs.unsqueeze(1)
+    if log_probs.dim() != 3:
+        raise RuntimeError("log_probs must be (T,B,C) or (T,C)")
+    dev = _rt.device(log_probs)
+    lp = log_probs.to(device=dev, dtype=torch.float32)
+    if lp.stride(2) != 1:
+        lp = lp.contiguous()
+    T, B, C = lp.shape
+    if not (0 <= blank < C):
+        raise RuntimeError("blank must be in label range")
+    il, il_host = _as_len_tensor(input_lengths, dev)
+    tl, tl_host = _as_len_tensor(target_lengths, dev)
+    if il.numel() != B or tl.numel() != B:
+        raise RuntimeError("input_lengths and target_lengths must have size batch_size")
+    tg = targets.to(device=dev, dtype=torch.int64).contiguous()
+    if tg.dim() == 2:
+        if tg.size(0) != B:
+            raise RuntimeError("targets must be (B, Lmax) or 1-D")
+        lmax, tstride = tg.size(1), tg.size(1)
+    elif tg.dim() == 1:
+        # concatenated targets: the padding width is not known on the host without reading the lengths
+        src = tl_host if tl_host is not None else tl.cpu()
+        lmax, tstride = (int(src.max()) if B else 0), 0
+        tl_host = src
+    else:
+        raise RuntimeError("targets must be 1-D or 2-D")
+    if validate:
+        # torch validates on the host (aten reads the lengths); do the same when they are host-visible for free,
+        # otherwise after the launch through the status vector.
+        if il_host is not None and B and (int(il_host.max()) > T or int(il_host.min()) < 0):
+            raise RuntimeError("Expected input_lengths to have value at most %d and be non-negative" % T)
+        if tl_host is not None and B:
+            if int(tl_host.min()) < 0 or (tg.dim() == 2 and int(tl_host.max()) > lmax):
+                raise RuntimeError("Expected target_lengths to be non-negative and at most the padded target width")
+            if tg.dim() == 1 and int(tl_host.sum()) > tg.numel():
+                raise RuntimeError("Expected the concatenated targets to hold sum(target_lengths) labels")
+    nll = torch.empty(B, dtype=torch.float32, device=dev) if nll is None else nll
+    if want_grad and grad is None:
+        grad = torch.empty((T, B, C), dtype=torch.float32, device=dev)
+    status = torch.empty(B, dtype=torch.int32, device=dev) if status is None else status
+    need = _lib.C.c_size_t(0)
+    _lib.check(L.mdd_ctc_loss_workspace_bytes(T, B, C, lmax, algo, _lib.C.byref(need)), "mdd_ctc_loss_workspace_bytes")
+    ws = _rt.workspace(need.value, dev, "ctc")
+    go = None if grad_out is None else grad_out.to(device=dev, dtype=torch.float32).contiguous()
+    rc = L.mdd_ctc_loss(lp.data_ptr(), T, B, C, lp.stride(0), lp.stride(1), _rt.ptr(tg), tstride, il.data_ptr(),
+                        tl.data_ptr(), lmax, blank, int(bool(zero_infinity)), _rt.ptr(go), float(grad_scalar),
+                        nll.data_ptr(), _rt.ptr(grad if want_grad else None), _rt.ptr(loss_sum), status.data_ptr(),
+                        algo, ws.data_ptr(), ws.numel(), _rt.stream_ptr(dev))
+    _lib.check(rc, "mdd_ctc_loss")
+    if validate and (il_host is None or tl_host is None):
+        if bool((status != 0).any()):
+            raise RuntimeError("ctc_loss: input_lengths/target_lengths/targets out of range (status %s)"
+                               % status.nonzero().flatten()[:8].tolist())
+    return nll, (grad if want_grad else None), status
+
+
+class _CTCLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, log_probs, targets, input_lengths, target_lengths, blank, zero_infinity, algo, validate):
+        want = ctx.needs_input_grad[0]
+        nll, grad, _ = ctc_loss_raw(log_probs.detach(), targets, input_lengths, target_lengths, blank, zero_infinity,
+                                    want_grad=want, algo=algo, validate=validate)
+        ctx.grad_buf = grad
+        ctx.in_shape = tuple(log_probs.shape)
+        ctx.in_dtype = log_probs.dtype
+        ctx.in_device = log_probs.device
+        return nll
+
+    @staticmethod
+    def backward(ctx, g):
+        grad = ctx.grad_buf
+        if grad is None:
+            raise RuntimeError("CTCLoss: the gradient buffer of this forward was already consumed "
+                               "(backward through the same graph twice is not supported)")
+        ctx.grad_buf = None
+        T, B, C = grad.shape
+        dev = grad.device
+        scale = g.to(device=dev, dtype=torch.float32).expand(B).contiguous()
+        L = _lib.lib()
+        _lib.check(L.mdd_ctc_scale_grad(grad.data_ptr(), T, B, C, scale.data_ptr(), 1.0, _rt.stream_ptr(dev)),
+                   "mdd_ctc_scale_grad")
+        out = grad
+        if len(ctx.in_shape) == 2:
+            out = out.squeeze(1)
+        out = out.to(device=ctx.in_device, dtype=ctx.in_dtype)
+        return out, None, None, None, None, None, None, None
+
+
+def ctc_loss(log_probs, targets, input_lengths, target_lengths, blank=0, reduction="mean", zero_infinity=False,
+             algo=0, validate=True):
+    """torch.nn.functional.ctc_loss-compatible functional form."""
+    if reduction not in ("none", "mean", "sum"):
+        raise ValueError("%s is not a valid value for reduction" % reduction)
+    nll = _CTCLossFn.apply(log_probs, targets, input_lengths, target_lengths, int(blank), bool(zero_infinity),
+                           int(algo), bool(validate))
+    if log_probs.dim() == 2 and reduction == "none":
+        nll_out = nll.squeeze(0)
+    else:
+        nll_out = nll
+    if reduction == "none":
+        out = nll_out
+    elif reduction == "sum":
+        out = nll.sum()
+    else:
+        tl = target_lengths if isinstance(target_lengths, torch.Tensor) else torch.as_tensor(list(target_lengths))
+        tl = tl.to(device=nll.device, dtype=nll.dtype).clamp_min(1)
+        out = (nll / tl).mean()
+    if log_probs.dtype != torch.float32:
+        out = out.to(log_probs.dtype)
+    if not log_probs.is_cuda:
+        out = out.to(log_probs.device)
+    return out
+
+
+class CTCLoss(torch.nn.Module):
+    """Same constructor and call signature as torch.nn.CTCLoss (train_ctc.py:186 builds it with reduction='sum')."""
+
+    def __init__(self, blank: int = 0, reduction: str = "mean", zero_infinity: bool = False, algo: int = 0,
+                 validate: bool = True):
+        super().__init__()
+        self.blank = blank
+        self.reduction = reduction
+        self.zero_infinity = zero_infinity
+        self.algo = algo
+        self.validate = validate
+
+    def forward(self, log_probs, targets, input_lengths, target_lengths):
+        return ctc_loss(log_probs, targets, input_lengths, target_lengths, self.blank, self.reduction,
+                        self.zero_infinity, self.algo, self.validate)

@@ -1,0 +1,496 @@
+"""GPU parity tests: the CUDA path (through the C ABI / the Python drop-ins) against the CPU oracle, the committed
+golden fixtures recorded from the real reference, and torch CPU ctc_loss.  Run on the B200 box: pytest -m gpu.
+
+Tolerances (BASELINE.json north_star): loss 1e-5 relative, gradient 1e-4 absolute in fp32 against torch CPU CTCLoss;
+decoded strings, alignments and MDD labels bit-exact."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import jload, npz
+from oracle import api as O
+
+pytestmark = pytest.mark.gpu
+
+LOSS_RTOL = 1e-5
+GRAD_ATOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def M():
+    import mddctc
+    assert torch.cuda.is_available()
+    mddctc._lib.lib()          # fails loudly if libmddctc.so is missing
+    return mddctc
+
+
+def _torch_cpu_ctc(lp, tg, il, tl, zero_inf=False, dtype=torch.float32):
+    x = lp.detach().cpu().to(dtype).clone().requires_grad_(True)
+    nll = torch.nn.functional.ctc_loss(x, tg.cpu(), il.cpu(), tl.cpu(), blank=0, reduction="none", zero_infinity=zero_inf)
+    nll.sum().backward()
+    return nll.detach(), x.grad
+
+
+def _check_ctc(M, lp, tg, il, tl, zero_inf=False, algo=0):
+    from mddctc.loss import ctc_loss_raw
+    nll, grad, st = ctc_loss_raw(lp.cuda(), tg.cuda(), il.cuda(), tl.cuda(), zero_infinity=zero_inf, algo=algo)
+    ref_nll, ref_grad = _torch_cpu_ctc(lp, tg, il, tl, zero_inf)
+    ref64_nll, ref64_grad = _torch_cpu_ctc(lp, tg, il, tl, zero_inf, torch.float64)
+    nll, grad = nll.cpu(), grad.cpu()
+    fin = torch.isfinite(ref_nll)
+    assert torch.equal(torch.isfinite(nll), fin)
+    assert torch.equal(nll[~fin], ref_nll[~fin])
+    # fp32 torch itself carries rounding noise of a few 1e-7 relative on long sequences: compare against both
+    np.testing.assert_allclose(nll[fin].numpy(), ref64_nll[fin].numpy(), rtol=LOSS_RTOL)
+    np.testing.assert_allclose(nll[fin].numpy(), ref_nll[fin].numpy(), rtol=LOSS_RTOL)
+    assert torch.equal(torch.isnan(grad), torch.isnan(ref_grad))
+    ok = ~torch.isnan(ref_grad)
+    assert float((grad[ok] - ref_grad[ok]).abs().max()) <= GRAD_ATOL
+    assert float((grad[ok].double() - ref64_grad[ok]).abs().max()) <= GRAD_ATOL
+    return nll, grad
+
+
+@pytest.mark.parametrize("algo", [1, 0])
+@pytest.mark.parametrize("name", ["basic", "repeat_ragged", "one_d", "infeasible", "infeasible_zi", "c42", "tiny"])
+def test_ctc_golden(M, name, algo):
+    z = npz("ctc_small.npz")
+    g = lambda k: z[name + "/" + k]
+    from mddctc.loss import ctc_loss_raw
+    zi = bool(g("zero_inf"))
+    nll, grad, st = ctc_loss_raw(torch.from_numpy(g("lp")).cuda(), torch.from_numpy(g("targets")).cuda(),
+                                 torch.from_numpy(g("in_len")).cuda(), torch.from_numpy(g("tgt_len")).cuda(),
+                                 zero_infinity=zi, algo=algo)
+    nll, grad = nll.cpu().numpy(), grad.cpu().numpy()
+    want, wg = g("nll_f32"), g("grad_f32")
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(nll), fin) and np.array_equal(nll[~fin], want[~fin])
+    np.testing.assert_allclose(nll[fin], want[fin], rtol=LOSS_RTOL)
+    np.testing.assert_allclose(nll[fin], g("nll_f64")[fin], rtol=LOSS_RTOL)
+    assert np.array_equal(np.isnan(grad), np.isnan(wg))
+    np.testing.assert_allclose(grad, wg, rtol=0, atol=GRAD_ATOL, equal_nan=True)
+    np.testing.assert_allclose(grad, g("grad_f64"), rtol=0, atol=GRAD_ATOL, equal_nan=True)
+
+
+@pytest.mark.parametrize("algo", [1, 0])
+def test_ctc_config2_vs_torch_cpu(M, algo):
+    """BASELINE config 2: T=200, B=32, C=42, L=30, plus the ragged / repeat / infeasible variant."""
+    g = torch.Generator().manual_seed(0)
+    lp = torch.log_softmax(torch.randn(200, 32, 42, generator=g), -1)
+    tg = torch.randint(1, 42, (32, 30), generator=g)
+    full_i, full_t = torch.full((32,), 200), torch.full((32,), 30)
+    _check_ctc(M, lp, tg, full_i, full_t, algo=algo)
+    il = torch.randint(100, 201, (32,), generator=g)
+    tl = torch.randint(10, 31, (32,), generator=g)
+    tg2 = tg.clone()
+    tg2[:, 1::2] = tg2[:, 0::2]                     # forced repeats l_i == l_{i+1}
+    il[5], tl[5] = 20, 30                           # infeasible: T_b < L_b + repeats
+    tl[7] = 0
+    _check_ctc(M, lp, tg2, il, tl, algo=algo)
+    _check_ctc(M, lp, tg2, il, tl, zero_inf=True, algo=algo)
+
+
+@pytest.mark.parametrize("algo", [1, 0])
+def test_ctc_config3_slice_vs_torch_cpu(M, algo):
+    """BASELINE config 3 shape on a B=48 slice (torch CPU finishes in seconds): T=1000, C=42, L=120."""
+    g = torch.Generator().manual_seed(1)
+    lp = torch.log_softmax(torch.randn(1000, 48, 42, generator=g), -1)
+    tg = torch.randint(1, 42, (48, 120), generator=g)
+    il = torch.full((48,), 1000)
+    tl = torch.full((48,), 120)
+    il[40:] = torch.randint(300, 1000, (8,), generator=g)
+    tl[44:] = torch.randint(1, 120, (4,), generator=g)
+    _check_ctc(M, lp, tg, il, tl, algo=algo)
+
+
+@pytest.mark.parametrize("C", [43, 45, 5, 64])
+def test_ctc_other_class_counts(M, C):
+    g = torch.Generator().manual_seed(C)
+    T, B, L = 150, 9, 20
+    lp = torch.log_softmax(torch.randn(T, B, C, generator=g), -1)
+    tg = torch.randint(1, C, (B, L), generator=g)
+    il = torch.randint(60, T + 1, (B,), generator=g)
+    tl = torch.randint(0, L + 1, (B,), generator=g)
+    for algo in (1, 0):
+        _check_ctc(M, lp, tg, il, tl, algo=algo)
+
+
+def test_ctc_peaky_and_extreme_inputs(M):
+    """Peaky posteriors (trained-model like) and rows with log-probs down to -80: the fast path must either stay within
+    tolerance or hand the utterance to the log-space kernel."""
+    g = torch.Generator().manual_seed(77)
+    T, B, C, L = 300, 16, 42, 40
+    x = torch.randn(T, B, C, generator=g)
+    x[:, :, 0] += 6 * (torch.rand(T, B, generator=g) < 0.7)
+    idx = torch.randint(1, C, (T, B), generator=g)
+    x.scatter_add_(2, idx[..., None], 9 * torch.ones(T, B, 1))
+    x[::7] *= 8                                     # some frames with huge dynamic range
+    lp = torch.log_softmax(x, -1)
+    tg = torch.randint(1, C, (B, L), generator=g)
+    il = torch.full((B,), T)
+    tl = torch.randint(5, L + 1, (B,), generator=g)
+    _check_ctc(M, lp, tg, il, tl, algo=0)
+    _check_ctc(M, lp, tg, il, tl, algo=1)
+
+
+def test_ctc_full_config3_properties(M):
+    """Full BASELINE config 3 (T=1000, B=4096, C=42, L=120): size-independent properties + a 16-utterance slice vs torch."""
+    from mddctc.loss import ctc_loss_raw
+    g = torch.Generator().manual_seed(1)
+    T, B, C, L = 1000, 4096, 42, 120
+    lp = torch.log_softmax(torch.randn(T, B, C, generator=g), -1)
+    tg = torch.randint(1, C, (B, L), generator=g)
+    il = torch.full((B,), T)
+    il[::5] = torch.randint(500, T, (len(il[::5]),), generator=g)
+    tl = torch.full((B,), L)
+    d = lp.cuda()
+    nll, grad, st = ctc_loss_raw(d, tg.cuda(), il.cuda(), tl.cuda())
+    assert int(st.abs().sum()) == 0
+    assert bool(torch.isfinite(nll).all())
+    # rows of the gradient sum to ~0 (softmax prob - occupancy, both sum to 1) for valid frames, exactly 0 beyond T_b
+    rs = grad.sum(-1)
+    assert float(rs.abs().max()) < 5e-4
+    tmask = torch.arange(T, device="cuda")[:, None] >= il.cuda()[None, :]
+    assert float(grad.abs().sum(-1)[tmask].max()) == 0.0
+    # determinism: bitwise identical on a second run
+    nll2, grad2, _ = ctc_loss_raw(d, tg.cuda(), il.cuda(), tl.cuda())
+    assert torch.equal(nll, nll2) and torch.equal(grad, grad2)
+    sel = torch.arange(0, B, 256)
+    ref_nll, ref_grad = _torch_cpu_ctc(lp[:, sel], tg[sel], il[sel], tl[sel])
+    np.testing.assert_allclose(nll[sel.cuda()].cpu().numpy(), ref_nll.numpy(), rtol=LOSS_RTOL)
+    assert float((grad[:, sel.cuda()].cpu() - ref_grad).abs().max()) <= GRAD_ATOL
+
+
+def test_ctcloss_module_autograd(M):
+    """The call pattern of train_ctc.py:72-96: reduction='sum', in-place division by the batch size, backward."""
+    from mddctc.loss import CTCLoss
+    g = torch.Generator().manual_seed(5)
+    T, B, C, L = 120, 8, 42, 25
+    logits = torch.randn(T, B, C, generator=g)
+    tg = torch.randint(1, C, (B, L), generator=g)
+    il = torch.randint(80, T + 1, (B,), generator=g)
+    tl = torch.randint(5, L + 1, (B,), generator=g)
+    for red in ("sum", "mean", "none"):
+        a = logits.clone().cuda().requires_grad_(True)
+        out = CTCLoss(reduction=red)(torch.log_softmax(a, -1), tg.cuda(), il.cuda(), tl.cuda())
+        if red == "sum":
+            out /= B
+        (out.sum()).backward()
+        b = logits.clone().requires_grad_(True)
+        ref = torch.nn.CTCLoss(reduction=red)(torch.log_softmax(b, -1), tg, il, tl)
+        if red == "sum":
+            ref /= B
+        ref.sum().backward()
+        np.testing.assert_allclose(out.detach().cpu().numpy(), ref.detach().numpy(), rtol=LOSS_RTOL)
+        assert float((a.grad.cpu() - b.grad).abs().max()) <= GRAD_ATOL
+    with pytest.raises(RuntimeError):
+        CTCLoss()(torch.log_softmax(logits, -1).cuda(), tg.cuda(), (il + 1000).cuda(), tl.cuda())
+    # tuple lengths + 1-D targets + (T,C) input
+    lp1 = torch.log_softmax(logits[:, 0], -1)
+    out = CTCLoss(reduction="sum")(lp1.cuda(), tg[0, :7].cuda(), (T,), (7,))
+    ref = torch.nn.CTCLoss(reduction="sum")(lp1, tg[0, :7], (T,), (7,))
+    np.testing.assert_allclose(float(out), float(ref), rtol=LOSS_RTOL)
+
+
+# ----------------------------------------------------------------------------------------------------- greedy
+def test_greedy_golden(M):
+    from mddctc.decoder import GreedyDecoder
+    z, js = npz("greedy.npz"), jload("greedy.json.gz")
+    for i, case in js.items():
+        voc = {int(k): v for k, v in case["vocab"].items()}
+        dec = GreedyDecoder(voc, space_idx=-1, blank_index=0)
+        assert dec.decode(torch.from_numpy(z[i + "/lp"]), z[i + "/lens"].tolist()) == case["out"], i
+        assert dec.decode(torch.from_numpy(z[i + "/lp"]).cuda(), z[i + "/lens"].tolist()) == case["out"], i
+
+
+def test_greedy_random_vs_oracle(M, vocab43):
+    from mddctc.decoder import GreedyDecoder
+    rng = np.random.default_rng(3)
+    dec = GreedyDecoder(vocab43, space_idx=-1, blank_index=0)
+    for T, B in ((500, 64), (37, 5), (129, 131), (1, 1)):
+        x = rng.standard_normal((T, B, 43)).astype(np.float32)
+        x = np.round(x * 2) / 2                       # exact ties
+        run = rng.integers(0, 43, size=(T, B))
+        for t in range(1, T):
+            keep = rng.random(B) < 0.7
+            run[t, keep] = run[t - 1, keep]
+        x[np.arange(T)[:, None], np.arange(B)[None, :], run] += 2.5
+        lens = rng.integers(0, T + 1, size=B)
+        want = O.greedy_decode(x, lens, vocab43)
+        assert dec.decode(torch.from_numpy(x), lens.tolist()) == want
+        tokens, out_len, amax = dec.decode_tokens(torch.from_numpy(x).cuda(), lens.tolist())
+        assert torch.equal(amax[:T].long().cpu(), torch.from_numpy(x).argmax(-1))
+
+
+def test_greedy_full_size_properties(M, vocab43):
+    """Config-3-sized stream (T=1000, B=4096): argmax equals torch's, collapse is idempotent and length-consistent."""
+    from mddctc.decoder import GreedyDecoder
+    g = torch.Generator(device="cuda").manual_seed(4)
+    T, B, C = 1000, 4096, 43
+    lp = torch.randn(T, B, C, device="cuda", generator=g)
+    lens = torch.randint(50, T + 1, (B,), device="cuda", generator=g)
+    dec = GreedyDecoder(vocab43, space_idx=-1, blank_index=0)
+    tokens, out_len, amax = dec.decode_tokens(lp, lens)
+    assert torch.equal(amax.long(), lp.argmax(-1))
+    assert int(out_len.max()) <= T and int(out_len.min()) >= 0
+    sel = [0, 17, 4095]
+    want_tok, want_len, _ = O.greedy_tokens(lp[:, sel].cpu().numpy(), lens[sel].cpu().numpy())
+    for j, b in enumerate(sel):
+        assert int(out_len[b]) == int(want_len[j])
+        assert tokens[b, :out_len[b]].cpu().tolist() == want_tok[j, :want_len[j]].tolist()
+
+
+# ----------------------------------------------------------------------------------------------------- Levenshtein
+def test_wer_corpus_totals(M):
+    """Known-answer totals recorded by the reference's own runs."""
+    from mddctc.decoder import Decoder
+    dec = Decoder({0: "blank"}, space_idx=-1, blank_index=0)
+    data = jload("wer_corpus.json.gz")
+    for name, c in data.items():
+        res = dec.wer_batch(c["hyp"], c["ref"])
+        assert sum(r[0] for r in res) == c["total"], name
+        assert [r[0] for r in res] == c["dist"]
+        if c["paths"]:
+            assert ["".join(r[1]) for r in res] == c["paths"]
+    d2 = Decoder({0: "blank"}, space_idx=-1, blank_index=0, variant="cnn-rnn-ctc")
+    c = data["cnn_rnn_hyp_human"]
+    assert sum(d2.wer_batch(c["hyp"], c["ref"])) == 7934
+
+
+def test_wer_single_call_semantics(M):
+    from mddctc.decoder import Decoder
+    dec = Decoder({0: "blank"}, space_idx=-1, blank_index=0)
+    assert dec.wer("a b c d", "a x c e f") == (3, ["-", "S", "-", "D", "S"])
+    assert dec.wer("a b c", "b c d") == (2, ["I", "-", "-", "D"])
+    with pytest.raises(TypeError):
+        dec.wer("", "a b")
+    assert dec.cer("kitten", "sitting") == 3
+
+
+def test_edit_align_random_vs_oracle(M):
+    from mddctc.decoder import edit_align_tokens
+    rng = np.random.default_rng(8)
+    for (B, Lh, Lr, V) in ((300, 40, 40, 6), (64, 200, 190, 40), (40, 33, 500, 3), (16, 700, 650, 12), (50, 1, 1, 2)):
+        hl = rng.integers(0, Lh + 1, size=B).astype(np.int32)
+        rl = rng.integers(0, Lr + 1, size=B).astype(np.int32)
+        H = rng.integers(0, V, size=(B, Lh)).astype(np.int32)
+        R = rng.integers(0, V, size=(B, Lr)).astype(np.int32)
+        for b in range(0, B, 3):                     # correlated pairs
+            n = min(hl[b], rl[b])
+            H[b, :n] = R[b, :n]
+            flip = rng.random(n) < 0.2
+            H[b, :n][flip] = rng.integers(0, V, size=int(flip.sum()))
+        dist, paths, st = O.edit_align([H[b, :hl[b]].tolist() for b in range(B)], [R[b, :rl[b]].tolist() for b in range(B)])
+        r = edit_align_tokens(torch.from_numpy(H).cuda(), torch.from_numpy(hl).cuda(), torch.from_numpy(R).cuda(),
+                              torch.from_numpy(rl).cuda(), Lh, Lr, want_ops=True)
+        assert r["dist"].cpu().numpy().tolist() == dist.tolist()
+        assert r["status"].cpu().numpy().tolist() == st.tolist()
+        ops, ol = r["ops"].cpu().numpy(), r["ops_len"].cpu().numpy()
+        for b in range(B):
+            assert "".join(chr(c) for c in ops[b, :ol[b]]) == "".join(paths[b]), (B, Lh, Lr, b)
+
+
+def test_compute_wer_vs_oracle(M):
+    from mddctc.mdd import compute_wer
+    rng = np.random.default_rng(12)
+    B, T, Lmax = 32, 200, 30
+    idx = rng.integers(0, 42, size=(B, T))
+    for t in range(1, T):
+        keep = rng.random(B) < 0.6
+        idx[keep, t] = idx[keep, t - 1]
+    idx[rng.random((B, T)) < 0.4] = 0
+    il = rng.integers(100, T + 1, size=B)
+    tg = rng.integers(1, 42, size=(B, Lmax))
+    tl = rng.integers(1, Lmax + 1, size=B)
+    assert compute_wer(idx, il, tg, tl) == O.compute_wer(idx, il, tg, tl)
+
+
+# ----------------------------------------------------------------------------------------------------- beam search
+def test_beam_golden_small(M, arpa):
+    from mddctc.decoder import BeamDecoder
+    z, meta = npz("beam_small.npz"), jload("beam_small.json.gz")
+    exc = {"IndexError": IndexError, "ValueError": ValueError, "KeyError": KeyError}
+    for i, m in enumerate(meta):
+        voc = {k: w for k, w in enumerate(m["vocab"])}
+        dec = BeamDecoder(voc, beam_width=m["W"], blank_index=0, space_idx=-1, lm_path=arpa, lm_alpha=m["alpha"])
+        probs = torch.from_numpy(z[str(i)][None])
+        if isinstance(m["out"], dict):
+            with pytest.raises(exc[m["out"]["exc"]]):
+                dec.decode_probs(probs, [m["len"]])
+        else:
+            assert dec.decode_probs(probs, [m["len"]]) == [m["out"]], i
+
+
+def test_beam_golden_c4(M, arpa, vocab43):
+    from mddctc.decoder import BeamDecoder
+    z, meta = npz("beam_c4.npz"), jload("beam_c4.json.gz")
+    for alpha in (0.0, 0.3):
+        dec = BeamDecoder(vocab43, beam_width=10, blank_index=0, space_idx=-1, lm_path=arpa, lm_alpha=alpha)
+        want = meta["out_alpha_%g" % alpha]
+        assert all(isinstance(w, str) for w in want)
+        assert dec.decode_probs(torch.from_numpy(z["probs"]), meta["lens"]) == want
+        # through the log-prob entry point with CPU tensors (torch CPU exp, the reference's own boundary)
+        lp = torch.log(torch.from_numpy(z["probs"])).transpose(0, 1).contiguous()
+        if torch.equal(torch.exp(lp.transpose(0, 1)), torch.from_numpy(z["probs"])):
+            assert dec.decode(lp, meta["lens"]) == want
+
+
+def _peaky(rng, B, T, C):
+    x = rng.standard_normal((B, T, C)).astype(np.float32)
+    u = rng.random((B, T))
+    k = rng.integers(1, C, size=(B, T))
+    bi, ti = np.nonzero(u < 0.7)
+    x[bi, ti, 0] += 8
+    bi, ti = np.nonzero(u >= 0.7)
+    x[bi, ti, k[bi, ti]] += 6
+    return torch.exp(torch.log_softmax(torch.from_numpy(x), -1)).numpy()
+
+
+@pytest.mark.parametrize("alpha", [0.0, 0.3])
+def test_beam_random_vs_oracle(M, arpa, vocab43, alpha):
+    """C4-shaped inputs (peaky posteriors, beam 10) + dense random + quantised ties, against the C oracle."""
+    from mddctc.decoder import BeamDecoder
+    rng = np.random.default_rng(31)
+    lm = O.lm_table(arpa, vocab43, 43)
+    dec = BeamDecoder(vocab43, beam_width=10, blank_index=0, space_idx=-1, lm_path=arpa, lm_alpha=alpha)
+    probs = _peaky(rng, 96, 500, 43)
+    dense = torch.softmax(torch.from_numpy(rng.standard_normal((32, 120, 43)).astype(np.float32)), -1).numpy()
+    ties = torch.softmax(torch.from_numpy(np.round(rng.standard_normal((32, 60, 43))).astype(np.float32)), -1).numpy()
+    for P in (probs, dense, ties):
+        B, T, _ = P.shape
+        lens = rng.integers(T // 2, T + 1, size=B)
+        toks, olen, st, score = O.beam_tokens(P, lens, 10, 0, lm, alpha)
+        t2, l2, s2, sc2 = dec.decode_probs_tokens(torch.from_numpy(P), lens.tolist())
+        t2, l2, s2, sc2 = t2.cpu().numpy(), l2.cpu().numpy(), s2.cpu().numpy(), sc2.cpu().numpy()
+        assert s2.tolist() == st.tolist()
+        assert l2.tolist() == olen.tolist()
+        for b in range(B):
+            assert t2[b, :l2[b]].tolist() == toks[b, :olen[b]].tolist(), b
+        ok = st == 0
+        np.testing.assert_allclose(sc2[ok], score[ok], rtol=1e-12)
+
+
+def test_beam_wide_beam(M, arpa, vocab43):
+    """The reference's default beam width (200) on a short utterance."""
+    from mddctc.decoder import BeamDecoder
+    rng = np.random.default_rng(32)
+    lm = O.lm_table(arpa, vocab43, 43)
+    P = torch.softmax(torch.from_numpy(rng.standard_normal((3, 25, 43)).astype(np.float32)) * 2, -1).numpy()
+    dec = BeamDecoder(vocab43, beam_width=200, blank_index=0, space_idx=-1, lm_path=arpa, lm_alpha=0.01)
+    toks, olen, st, _ = O.beam_tokens(P, [25, 25, 25], 200, 0, lm, 0.01)
+    t2, l2, s2, _ = dec.decode_probs_tokens(torch.from_numpy(P), [25, 25, 25])
+    assert s2.cpu().tolist() == st.tolist() and l2.cpu().tolist() == olen.tolist()
+    for b in range(3):
+        assert t2[b, :olen[b]].cpu().tolist() == toks[b, :olen[b]].tolist()
+
+
+# ----------------------------------------------------------------------------------------------------- MDD
+def _tok(vocab_inv, s):
+    return [vocab_inv[w] for w in s.split()]
+
+
+def test_mdd_post_golden(M, vocab43):
+    """wer -> align_canonical_decoded -> stastics -> score on 600 noisy pairs + the KATs of SURVEY Appendix B."""
+    from mddctc.mdd import MDDScorer, align_canonical_decoded, print_aligned_string, stastics
+    cases = jload("mdd_post.json.gz")
+    inv = {w: k for k, w in vocab43.items()}
+    sc = MDDScorer(vocab43)
+    dec = [_tok(inv, c["decoded"]) for c in cases]
+    can = [_tok(inv, c["canonical"]) for c in cases]
+    B = len(cases)
+    Ld, Lc = max(max(map(len, dec)), 1), max(max(map(len, can)), 1)
+    D = np.zeros((B, Ld), np.int32); Cn = np.zeros((B, Lc), np.int32)
+    for b in range(B):
+        D[b, :len(dec[b])] = dec[b]; Cn[b, :len(can[b])] = can[b]
+    r = sc.align_tokens(torch.from_numpy(D).cuda(), torch.tensor([len(x) for x in dec], dtype=torch.int32).cuda(),
+                        torch.from_numpy(Cn).cuda(), torch.tensor([len(x) for x in can], dtype=torch.int32).cuda())
+    got = sc.to_python(r)
+    for b, c in enumerate(cases):
+        want = c["out"]
+        if "exc" in want:
+            assert isinstance(got[b], TypeError), b
+            continue
+        for k in ("path0", "dec", "can", "path", "ins", "sub", "del", "correct", "del_sub", "score"):
+            assert got[b][k] == want[k], (b, k, c["decoded"], c["canonical"])
+        assert list(print_aligned_string(got[b]["dec"], got[b]["can"], got[b]["path"])) == want["printed"]
+    # the literal single-utterance call surface of infer.py:335-340
+    for c in cases[:40]:
+        want = c["out"]
+        if "exc" in want:
+            continue
+        dn = " ".join(w for w in c["decoded"].split(" ") if w != "sil").replace("err", "").replace("  ", " ")
+        cn = " ".join(w for w in c["canonical"].split(" ") if w != "sil")
+        s1, s2, l = align_canonical_decoded([w for w in dn.split(" ") if w], [w for w in cn.split(" ") if w],
+                                            list(want["path0"]))
+        assert (s1, s2, l) == (want["dec"], want["can"], want["path"])
+        assert stastics(l, s2, s1) == (want["ins"], want["sub"], want["del"])
+
+
+def test_config1_words_end_to_end(M):
+    """BASELINE config 1: greedy decode + MDD alignment of the vocabulary/single word list against the reference run."""
+    from mddctc.decoder import GreedyDecoder
+    from mddctc.mdd import MDDScorer
+    z, js = npz("c1_words.npz"), jload("c1_words.json.gz")
+    voc = {k: w for k, w in enumerate(js["vocab"])}
+    inv = {w: k for k, w in voc.items()}
+    dec = GreedyDecoder(voc, space_idx=-1, blank_index=0)
+    lp = torch.from_numpy(z["lp"]).cuda()
+    lens = torch.from_numpy(z["lens"])
+    assert dec.decode(lp, lens.tolist()) == js["decoded"]
+    tokens, out_len, _ = dec.decode_tokens(lp, lens.tolist())
+    B = len(js["words"])
+    Lc = max(len(c) for c in js["canonical"])
+    Cn = np.zeros((B, Lc), np.int32)
+    for b, c in enumerate(js["canonical"]):
+        Cn[b, :len(c)] = [inv[w] for w in c]
+    sc = MDDScorer(voc)
+    r = sc.align_tokens(tokens, out_len, torch.from_numpy(Cn).cuda(),
+                        torch.tensor([len(c) for c in js["canonical"]], dtype=torch.int32).cuda())
+    got = sc.to_python(r)
+    for b, want in enumerate(js["mdd"]):
+        for k in ("path0", "dec", "can", "path", "ins", "sub", "del", "correct", "del_sub", "score"):
+            assert got[b][k] == want[k], (js["words"][b], k)
+
+
+# ----------------------------------------------------------------------------------------------------- prefix scorer
+def test_prefix_scorer_vs_oracle_and_invariant(M):
+    from mddctc.prefix import CTCPrefixScorer
+    g = torch.Generator().manual_seed(9)
+    T, B, C, W = 60, 3, 12, 4
+    x = torch.log_softmax(torch.randn(T, B, C, generator=g), -1)
+    lens = torch.tensor([60, 45, 31])
+    scorer = CTCPrefixScorer(x.cuda(), lens.cuda(), blank=0, beam=W)
+    labels = [[1, 2, 2, 5, 7], [3, 3, 3], [11, 1]]
+    # hypothesis w of utterance b follows labels[b] (rotated by w so that the W hypotheses differ)
+    state = scorer.initial_state()
+    seqs = [[list(np.roll(labels[b], w)) for w in range(W)] for b in range(B)]
+    nsteps = max(len(s) for s in labels)
+    r_or = [[O.prefix_init(x[:lens[b], b].double().numpy()) for w in range(W)] for b in range(B)]
+    last = [[-1] * W for _ in range(B)]
+    for n in range(nsteps):
+        psi, eos = scorer.score(state)
+        psi, eos = psi.cpu().numpy(), eos.cpu().numpy()
+        sel_h = torch.zeros((B, W), dtype=torch.int32)
+        sel_l = torch.zeros((B, W), dtype=torch.int32)
+        for b in range(B):
+            for w in range(W):
+                glen = min(n, len(seqs[b][w]))
+                want_psi, want_r, want_eos = O.prefix_score(x[:lens[b], b].double().numpy(), r_or[b][w], last[b][w], glen)
+                fin = np.isfinite(want_psi)
+                assert np.array_equal(np.isfinite(psi[b, w]), fin)
+                np.testing.assert_allclose(psi[b, w][fin], want_psi[fin], rtol=1e-5, atol=1e-5)
+                np.testing.assert_allclose(eos[b, w], want_eos, rtol=1e-5, atol=1e-5)
+                c = seqs[b][w][n] if n < len(seqs[b][w]) else None
+                sel_h[b, w] = w
+                sel_l[b, w] = c if c is not None else -1
+                if c is not None:
+                    r_or[b][w], last[b][w] = want_r[c], c
+        # hypotheses that are finished keep their state (label -1 is reported as invalid -> state of -inf, unused after)
+        keep = sel_l >= 0
+        state = scorer.advance(state, sel_h.cuda(), sel_l.cuda(), keep.cuda())
+    psi, eos = scorer.score(state)
+    for b in range(B):
+        nll = torch.nn.functional.ctc_loss(x[:, b:b + 1].double(), torch.tensor([labels[b]]), lens[b:b + 1],
+                                           torch.tensor([len(labels[b])]), reduction="none")
+        assert abs(float(eos[b, 0]) + float(nll)) < 1e-4 * max(1.0, abs(float(nll)))
