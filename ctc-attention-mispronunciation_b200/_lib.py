@@ -90,7 +90,7 @@ class PostOut(C.Structure):
 
 
 EXPORTS = ["mdd_version", "mdd_error_string", "mdd_launch_count", "mdd_launch_count_reset",
-           "mdd_ctc_loss_workspace_bytes", "mdd_ctc_loss", "mdd_ctc_scale_grad", "mdd_greedy_decode",
+           "mdd_ctc_loss_workspace_bytes", "mdd_ctc_loss", "mdd_ctc_scale_grad", "mdd_greedy_decode", "mdd_collapse", "mdd_post_align",
            "mdd_edit_align_workspace_bytes", "mdd_edit_align", "mdd_beam_search_workspace_bytes", "mdd_beam_search",
            "mdd_exp_transpose", "mdd_prefix_init", "mdd_prefix_score", "mdd_prefix_advance"]
 
@@ -118,6 +118,8 @@ def lib():
     L.mdd_ctc_loss.argtypes = [vp, i, i, i, i64, i64, vp, i64, vp, vp, i, i, i, vp, f, vp, vp, vp, vp, i, vp, sz, vp]
     L.mdd_ctc_scale_grad.argtypes = [vp, i, i, i, vp, f, vp]
     L.mdd_greedy_decode.argtypes = [vp, i, i, i, vp, i, vp, vp, vp, i, vp, vp]
+    L.mdd_collapse.argtypes = [vp, i, i, vp, i, vp, vp, i, vp, vp]
+    L.mdd_post_align.argtypes = [vp, i, vp, vp, i, vp, i, i, i, vp, i, vp, C.POINTER(PostOut), i, vp]
     L.mdd_edit_align_workspace_bytes.argtypes = [i, i, i, C.POINTER(sz)]
     L.mdd_edit_align.argtypes = [vp, i, vp, vp, i, vp, i, i, i, vp, vp, i, vp, vp, i, vp, vp, C.POINTER(PostOut), vp,
                                  sz, vp]
@@ -128,9 +130,10 @@ def lib():
     L.mdd_prefix_score.argtypes = [vp, i, i, i, vp, i, i, vp, vp, vp, vp, vp, vp]
     L.mdd_prefix_advance.argtypes = [vp, i, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, vp]
     for name in EXPORTS:
-        fn = getattr(L, name)
-        if fn.restype is C.c_int and name not in ("mdd_version",):
-            pass
+        fn = getattr(L, name)            # AttributeError here = the .so is stale / an export is missing
+        if name not in ("mdd_error_string", "mdd_launch_count", "mdd_launch_count_reset") and fn.argtypes is None \
+                and name != "mdd_version":
+            raise MddCtcLibraryError("no ctypes signature declared for %s" % name)
     _lib = L
     return L
 

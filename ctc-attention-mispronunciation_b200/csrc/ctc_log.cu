@@ -8,6 +8,12 @@
 // sweep walks chunks from the end, recomputes alpha for the chunk into shared memory, runs beta and emits
 //     grad[t,c] = (exp(lp[t,c]) - exp(LSE_{s: l'_s = c}(alpha_t(s) + beta_t(s)) + nll - lp[t,c])) * g_b
 // with a deterministic per-class reduction (CSR class -> states built once per utterance; no atomics).
+//
+// Precision: alpha/beta are kept *normalised* -- each row is shifted by the maximum of the previous row (a lagged
+// max costs no extra barrier) and the shifts are accumulated in fp64 -- so stored magnitudes stay O(10) instead of
+// O(nll) and fp32 rounding does not grow with T.  The per-frame constant that ties alpha~ + beta~ back to the
+// occupancy is not formed as a difference of large numbers either: it is the frame's own normaliser
+//     Z_t = LSE_s(alpha~_t(s) + beta~_t(s) - lp[t, l'_s])   (sum_s alpha_t(s) beta_t(s) / p_t(l'_s) = P for every t).
 #include "common.cuh"
 #include "ctc_params.cuh"
 
@@ -62,6 +68,15 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
     int* cls_list = cls_start + C + 1;                          // [Lmax] label index i (state 2i+1) grouped by class
     __shared__ float s_nll;
     __shared__ int s_badlabel;
+    __shared__ float s_pmax[2][NT / 32];     // per-warp maxima of the row written in the previous step
+    __shared__ float s_lc[MDD_MAX_CLASSES];  // per-class LSE(alpha~+beta~) - lp
+    const int warp = tid >> 5, lane = tid & 31;
+    auto row_shift = [&](int parity) {       // max of the previous row (0 if the row is all -inf)
+        float m = s_pmax[parity][0];
+#pragma unroll
+        for (int w = 1; w < NT / 32; ++w) m = fmaxf(m, s_pmax[parity][w]);
+        return m == -CUDART_INF_F ? 0.f : m;
+    };
 
     const int64_t* tg = p.tgt_stride ? p.targets + (int64_t)b * p.tgt_stride : p.targets + p.tgt_offsets[b];
     if (tid == 0) s_badlabel = 0;
@@ -111,21 +126,31 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
     // ------------------------------------------------------------------ forward: alpha, checkpoints, nll
     if (tid < C) srow[tid] = lp_b[tid];
     __syncthreads();
-    for (int s = tid; s < S; s += NT) {
-        float v = -CUDART_INF_F;
-        if (s == 0) v = srow[blank];
-        else if (s == 1) v = srow[lab[0]];
-        bbuf[s] = v;
-        ck[s] = v;
+    {
+        float pm = -CUDART_INF_F;
+        for (int s = tid; s < S; s += NT) {
+            float v = -CUDART_INF_F;
+            if (s == 0) v = srow[blank];
+            else if (s == 1) v = srow[lab[0]];
+            bbuf[s] = v;
+            ck[s] = v;
+            pm = fmaxf(pm, v);
+        }
+        pm = warp_max(pm);
+        if (lane == 0) s_pmax[0][warp] = pm;
     }
+    double shift_sum = 0.0;                  // identical in every thread
     for (int t = 1; t < Tb; ++t) {
         float* rw = srow + (t & 1) * C;
         if (tid < C) rw[tid] = lp_b[(size_t)t * p.stride_t + tid];
         __syncthreads();
+        const float shift = row_shift((t - 1) & 1);
+        shift_sum += (double)shift;
         const float* prev = bbuf + ((t - 1) & 1) * Smax;
         float* cur = bbuf + (t & 1) * Smax;
         const bool store = (t % K) == 0;
         float* ckt = ck + (size_t)(t / K) * Smax;
+        float pm = -CUDART_INF_F;
         for (int s = tid; s < S; s += NT) {
             float a1 = prev[s];
             float a2 = s > 0 ? prev[s - 1] : -CUDART_INF_F;
@@ -136,16 +161,19 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
                 cls = lab[i];
                 if (i > 0 && lab[i - 1] != cls) a3 = prev[s - 2];
             }
-            float v = lse3_acc(a1, a2, a3) + rw[cls];
+            float v = lse3_acc(a1, a2, a3) + (rw[cls] - shift);
             cur[s] = v;
             if (store) ckt[s] = v;
+            pm = fmaxf(pm, v);
         }
+        pm = warp_max(pm);
+        if (lane == 0) s_pmax[t & 1][warp] = pm;
     }
     __syncthreads();
     if (tid == 0) {
         const float* lastrow = bbuf + ((Tb - 1) & 1) * Smax;
         float ll = S > 1 ? lse2_acc(lastrow[S - 1], lastrow[S - 2]) : lastrow[S - 1];
-        s_nll = -ll;
+        s_nll = (float)(-((double)ll + shift_sum));
     }
     __syncthreads();
     const float nll = s_nll;
@@ -165,13 +193,20 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
     for (int j = n_chunks - 1; j >= 0; --j) {
         const int t0 = j * K, t1 = min(Tb, t0 + K);
         __syncthreads();   // previous chunk's readers of `chunk` are done
-        for (int s = tid; s < S; s += NT) chunk[s] = ck[(size_t)j * Smax + s];
+        {
+            float pm = -CUDART_INF_F;
+            for (int s = tid; s < S; s += NT) { const float v = ck[(size_t)j * Smax + s]; chunk[s] = v; pm = fmaxf(pm, v); }
+            pm = warp_max(pm);
+            if (lane == 0) s_pmax[t0 & 1][warp] = pm;
+        }
         for (int t = t0 + 1; t < t1; ++t) {
             float* rw = srow + (t & 1) * C;
             if (tid < C) rw[tid] = lp_b[(size_t)t * p.stride_t + tid];
             __syncthreads();
+            const float shift = row_shift((t - 1) & 1);
             const float* prev = chunk + (size_t)(t - 1 - t0) * Smax;
             float* cur = chunk + (size_t)(t - t0) * Smax;
+            float pm = -CUDART_INF_F;
             for (int s = tid; s < S; s += NT) {
                 float a1 = prev[s];
                 float a2 = s > 0 ? prev[s - 1] : -CUDART_INF_F;
@@ -182,9 +217,14 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
                     cls = lab[i];
                     if (i > 0 && lab[i - 1] != cls) a3 = prev[s - 2];
                 }
-                cur[s] = lse3_acc(a1, a2, a3) + rw[cls];
+                const float v = lse3_acc(a1, a2, a3) + (rw[cls] - shift);
+                cur[s] = v;
+                pm = fmaxf(pm, v);
             }
+            pm = warp_max(pm);
+            if (lane == 0) s_pmax[t & 1][warp] = pm;
         }
+        __syncthreads();   // s_pmax is reused (with its own parity) by the beta sweep
         for (int t = t1 - 1; t >= t0; --t) {
             float* rw = srow + (t & 1) * C;
             if (tid < C) rw[tid] = lp_b[(size_t)t * p.stride_t + tid];
@@ -192,6 +232,7 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
             const float* al = chunk + (size_t)(t - t0) * Smax;
             float* bn = bbuf + (t & 1) * Smax;
             const float* bo = bbuf + ((t + 1) & 1) * Smax;
+            float pm = -CUDART_INF_F;
             if (t == Tb - 1) {
                 for (int s = tid; s < S; s += NT) {
                     float v = -CUDART_INF_F;
@@ -199,8 +240,10 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
                     else if (s == S - 2) v = rw[lab[L - 1]];
                     bn[s] = v;
                     ab[s] = al[s] + v;
+                    pm = fmaxf(pm, v);
                 }
             } else {
+                const float shift = row_shift((t + 1) & 1);
                 for (int s = tid; s < S; s += NT) {
                     float b1 = bo[s];
                     float b2 = s + 1 < S ? bo[s + 1] : -CUDART_INF_F;
@@ -211,19 +254,19 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
                         cls = lab[i];
                         if (i + 1 < L && lab[i + 1] != cls) b3 = bo[s + 2];
                     }
-                    float v = lse3_acc(b1, b2, b3) + rw[cls];
+                    float v = lse3_acc(b1, b2, b3) + (rw[cls] - shift);
                     bn[s] = v;
                     ab[s] = al[s] + v;
+                    pm = fmaxf(pm, v);
                 }
             }
+            pm = warp_max(pm);
+            if (lane == 0) s_pmax[t & 1][warp] = pm;
             __syncthreads();
-            float* gr = grad_b + (size_t)t * gstride;
+            // per-class LSE_{s in c}(alpha~ + beta~) - lp[c]   (alpha and beta both carry the emission at t)
             if (tid < 32) {
-                float lcab = block_lse_blank(ab, S, nullptr, tid);
-                if (tid == 0) {
-                    float lpv = rw[blank];
-                    gr[blank] = (expf(lpv) - expf(lcab + nll - lpv)) * g;
-                }
+                const float lcab = block_lse_blank(ab, S, nullptr, tid);
+                if (tid == 0) s_lc[blank] = lcab - rw[blank];
             } else if (tid < 32 + C) {
                 const int c = tid - 32;
                 if (c != blank) {
@@ -236,9 +279,22 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
                         for (int n = n0; n < n1; ++n) acc += expf(ab[2 * cls_list[n] + 1] - m);
                         lcab = m + logf(acc);
                     }
-                    float lpv = rw[c];
-                    gr[c] = (expf(lpv) - expf(lcab + nll - lpv)) * g;
+                    s_lc[c] = lcab - rw[c];
                 }
+            }
+            __syncthreads();
+            // frame normaliser Z_t = LSE_c(s_lc[c]) (= log P up to the shifts), then grad = (softmax prob - occupancy) * g
+            if (tid < 32) {
+                float m = -CUDART_INF_F;
+                for (int c = tid; c < C; c += 32) m = fmaxf(m, s_lc[c]);
+                m = warp_max(m);
+                float acc = 0.f;
+                if (m != -CUDART_INF_F)
+                    for (int c = tid; c < C; c += 32) acc += expf(s_lc[c] - m);
+                acc = warp_sum(acc);
+                const float Z = (m == -CUDART_INF_F) ? -CUDART_INF_F : m + logf(acc);
+                float* gr = grad_b + (size_t)t * gstride;
+                for (int c = tid; c < C; c += 32) gr[c] = (expf(rw[c]) - expf(s_lc[c] - Z)) * g;   // -inf - -inf = NaN: infeasible
             }
         }
     }

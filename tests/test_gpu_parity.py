@@ -45,10 +45,13 @@ def _check_ctc(M, lp, tg, il, tl, zero_inf=False, algo=0):
     # fp32 torch itself carries rounding noise of a few 1e-7 relative on long sequences: compare against both
     np.testing.assert_allclose(nll[fin].numpy(), ref64_nll[fin].numpy(), rtol=LOSS_RTOL)
     np.testing.assert_allclose(nll[fin].numpy(), ref_nll[fin].numpy(), rtol=LOSS_RTOL)
-    assert torch.equal(torch.isnan(grad), torch.isnan(ref_grad))
+    assert torch.equal(torch.isnan(grad), torch.isnan(ref_grad)), (torch.isnan(grad).sum(), torch.isnan(ref_grad).sum())
     ok = ~torch.isnan(ref_grad)
-    assert float((grad[ok] - ref_grad[ok]).abs().max()) <= GRAD_ATOL
+    # truth = torch CPU fp64.  torch's own fp32 run carries rounding noise that grows with the magnitude of nll
+    # (its alpha/beta are unnormalised), so against it the bound is 1e-4 plus that run's own deviation from fp64.
+    dev32 = float((ref_grad[ok].double() - ref64_grad[ok]).abs().max()) if ok.any() else 0.0
     assert float((grad[ok].double() - ref64_grad[ok]).abs().max()) <= GRAD_ATOL
+    assert float((grad[ok] - ref_grad[ok]).abs().max()) <= GRAD_ATOL + dev32
     return nll, grad
 
 
@@ -157,9 +160,9 @@ def test_ctc_full_config3_properties(M):
     nll2, grad2, _ = ctc_loss_raw(d, tg.cuda(), il.cuda(), tl.cuda())
     assert torch.equal(nll, nll2) and torch.equal(grad, grad2)
     sel = torch.arange(0, B, 256)
-    ref_nll, ref_grad = _torch_cpu_ctc(lp[:, sel], tg[sel], il[sel], tl[sel])
+    ref_nll, ref_grad = _torch_cpu_ctc(lp[:, sel], tg[sel], il[sel], tl[sel], dtype=torch.float64)
     np.testing.assert_allclose(nll[sel.cuda()].cpu().numpy(), ref_nll.numpy(), rtol=LOSS_RTOL)
-    assert float((grad[:, sel.cuda()].cpu() - ref_grad).abs().max()) <= GRAD_ATOL
+    assert float((grad[:, sel.cuda()].cpu().double() - ref_grad).abs().max()) <= GRAD_ATOL
 
 
 def test_ctcloss_module_autograd(M):
@@ -177,13 +180,18 @@ def test_ctcloss_module_autograd(M):
         if red == "sum":
             out /= B
         (out.sum()).backward()
-        b = logits.clone().requires_grad_(True)
-        ref = torch.nn.CTCLoss(reduction=red)(torch.log_softmax(b, -1), tg, il, tl)
-        if red == "sum":
-            ref /= B
-        ref.sum().backward()
-        np.testing.assert_allclose(out.detach().cpu().numpy(), ref.detach().numpy(), rtol=LOSS_RTOL)
-        assert float((a.grad.cpu() - b.grad).abs().max()) <= GRAD_ATOL
+        refs = {}
+        for dt in (torch.float32, torch.float64):
+            b = logits.clone().to(dt).requires_grad_(True)
+            ref = torch.nn.CTCLoss(reduction=red)(torch.log_softmax(b, -1), tg, il, tl)
+            if red == "sum":
+                ref /= B
+            ref.sum().backward()
+            refs[dt] = (ref.detach(), b.grad)
+        np.testing.assert_allclose(out.detach().cpu().numpy(), refs[torch.float32][0].numpy(), rtol=LOSS_RTOL)
+        dev32 = float((refs[torch.float32][1].double() - refs[torch.float64][1]).abs().max())
+        assert float((a.grad.cpu().double() - refs[torch.float64][1]).abs().max()) <= GRAD_ATOL
+        assert float((a.grad.cpu() - refs[torch.float32][1]).abs().max()) <= GRAD_ATOL + dev32
     with pytest.raises(RuntimeError):
         CTCLoss()(torch.log_softmax(logits, -1).cuda(), tg.cuda(), (il + 1000).cuda(), tl.cuda())
     # tuple lengths + 1-D targets + (T,C) input
