@@ -1,10 +1,513 @@
-// ctc_fast.cu -- rescaled linear-domain CTC forward-backward (fast path).  Placeholder until the kernel lands:
-// reports "unsupported" so mdd_ctc_loss uses the log-space kernel for every utterance.
+// ctc_fast.cu -- rescaled linear-domain CTC forward-backward: the fast path of mdd_ctc_loss.
+//
+// Semantics: torch aten ctc_loss / _ctc_loss_backward as reached from nn.CTCLoss at
+// egs/attention_aug/steps/train_ctc.py:186,72,96 and egs/cnn-rnn-ctc/steps/train_ctc.py:148,51,67.
+//
+// Why not log space: a per-state log-sum-exp lattice needs ~7 MUFU ops per state-frame (S = 2L+1 = 241 states at
+// L = 120), which bounds the kernel at ~10 % of the HBM roofline on the SFU pipe alone.  Here the
+// emissions are exponentiated once per (t,c) and alpha/beta are propagated as plain products and sums (FADD/FMUL/
+// FFMA), renormalised every 4 frames to a fixed sum (2^32) with the log of the scale accumulated in fp64 for the
+// loss.  The occupancy is self-normalised per frame (Z_t = sum_s alpha_t(s) u_t(s)), so no scale bookkeeping enters the
+// gradient.  Utterances whose scales under/overflow (or that are infeasible, empty or malformed) set flags[b] and are
+// redone by the log-space kernel (ctc_log.cu) in the same stream: results never depend on this path being exact
+// for pathological inputs.
+//
+// Mapping: one warp per utterance, NSL consecutive lattice states per lane held in registers; the s-1 / s-2
+// neighbours across lanes come from one __shfl_up (alpha) or two __shfl_down (beta): no block barrier anywhere in the
+// recursion.  Eight warps (adjacent utterances, so their 168 B rows of one frame form one contiguous run in HBM)
+// share a CTA only to share the SM.
+//
+// Memory: the lattice never goes to HBM.  Forward sweep: log-prob rows are staged 16 frames at a time with cp.async
+// (double buffered), alpha enters each 16-frame chunk as a checkpoint row written to the workspace (S*4/16 B per
+// frame).  Backward sweep, chunks from the end: reload the chunk's rows (the last chunk is still in shared memory),
+// recompute alpha for 16 frames into shared memory, run beta; each frame's per-state occupancies overwrite the alpha
+// row, and a chunk-batched, deterministic class reduction (a class-sorted position list built once per utterance;
+// lanes = 16 frames x 2 halves of the list) produces grad = (p - occupancy / Z) * g for 16 rows at once.
 #include "common.cuh"
 #include "ctc_params.cuh"
 
 namespace mdd {
-bool ctc_fast_supported(int, int) { return false; }
-size_t ctc_fast_ws_bytes(int, int, int) { return 0; }
-int launch_ctc_fast(CtcParams, void*, cudaStream_t) { return MDD_E_UNSUPPORTED; }
+namespace {
+
+constexpr int KF = 16;                 // frames per chunk
+constexpr int RENORM_MASK = 3;         // renormalise after frames with (t & 3) == 3
+constexpr float TS = 4294967296.f;     // 2^32: renormalisation target for sum_s alpha~ (centres the fp32 range)
+constexpr float LOG_TS = 22.180709777918249f;
+constexpr float TINY = 1e-18f;         // scale sums below this hand the utterance to the log-space kernel
+
+__device__ __forceinline__ void cp_async4(void* dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int NSL>
+struct Geo {
+    static constexpr int NL = NSL / 2;            // label states per lane (odd j)
+    static constexpr int SLOTS = 32 * NSL;        // lattice slots per utterance
+    static constexpr int RS = SLOTS + 4;          // shared-memory row stride (floats): +4 keeps 16 B alignment and
+                                                  // spreads the 16 frame rows over banks for the class walk
+};
+
+// alpha~ row <-> registers.  Layout: float4 group g of lane l at (g*128 + 4*l): conflict-free 128-bit accesses.
+template <int NSL>
+__device__ __forceinline__ void row_store(float* row, int lane, const float (&a)[NSL]) {
+    if constexpr (NSL == 2) {
+        *reinterpret_cast<float2*>(row + 2 * lane) = make_float2(a[0], a[1]);
+    } else {
+#pragma unroll
+        for (int g = 0; g < NSL / 4; ++g)
+            *reinterpret_cast<float4*>(row + g * 128 + 4 * lane) = make_float4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3]);
+    }
+}
+template <int NSL>
+__device__ __forceinline__ void row_load(const float* row, int lane, float (&a)[NSL]) {
+    if constexpr (NSL == 2) {
+        const float2 v = *reinterpret_cast<const float2*>(row + 2 * lane);
+        a[0] = v.x; a[1] = v.y;
+    } else {
+#pragma unroll
+        for (int g = 0; g < NSL / 4; ++g) {
+            const float4 v = *reinterpret_cast<const float4*>(row + g * 128 + 4 * lane);
+            a[4 * g] = v.x; a[4 * g + 1] = v.y; a[4 * g + 2] = v.z; a[4 * g + 3] = v.w;
+        }
+    }
+}
+
+struct FastSmem {          // per-warp carve-up (floats / ints), computed on the host and in the kernel identically
+    int rows_off, occ_off, meta_off, zinv_off, lab_off, total_floats;
+};
+__host__ __device__ inline FastSmem fast_smem_layout(int NSL, int CP, int Lcap) {
+    FastSmem s;
+    int o = KF * (32 * NSL + 4);          // alpha~ chunk
+    s.rows_off = o; o += 2 * KF * CP;     // two staged row chunks
+    s.occ_off = o;  o += KF * CP;         // per-frame class occupancies
+    s.meta_off = o; o += Lcap;            // class-sorted position list
+    s.zinv_off = o; o += KF;
+    s.lab_off = o;  o += Lcap;            // labels
+    s.total_floats = (o + 3) & ~3;
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// One lattice step.  Lane l owns states s = NSL*l + j; even j = blank, odd j = label q = (j-1)/2.
+//   alpha: new[s] = (a[s] + a[s-1] + ma * a[s-2]) * e[s]        (ma = skip allowed into label s)
+//   beta : u[s]   =  b[s] + b[s+1] + mb * b[s+2];  new b[s] = u[s] * e[s]   (u = beta without the emission at t)
+// Label slots past the end of the target read a zero emission (row[C] = 0), which also keeps every later slot at 0.
+// ---------------------------------------------------------------------------------------------------------------
+template <int NSL>
+__device__ __forceinline__ void alpha_step(float (&a)[NSL], const float* __restrict__ row, int blank,
+                                           const int (&eidx)[NSL / 2], const float (&ma)[NSL / 2], int lane) {
+    float p = __shfl_up_sync(0xffffffffu, a[NSL - 1], 1);     // state NSL*l - 1 (a label state)
+    if (lane == 0) p = 0.f;
+    const float eb = row[blank];
+    float e[NSL / 2];
+#pragma unroll
+    for (int q = 0; q < NSL / 2; ++q) e[q] = row[eidx[q]];
+    float n[NSL];
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) {
+        const float m1 = j ? a[j - 1] : p;
+        if (j & 1) {
+            const float m2 = j >= 2 ? a[j - 2] : p;
+            n[j] = fmaf(ma[j >> 1], m2, a[j] + m1) * e[j >> 1];
+        } else {
+            n[j] = (a[j] + m1) * eb;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) a[j] = n[j];
+}
+
+template <int NSL>
+__device__ __forceinline__ void beta_step(float (&b)[NSL], float (&u)[NSL], const float* __restrict__ row, int blank,
+                                          const int (&eidx)[NSL / 2], const float (&mb)[NSL / 2], int lane) {
+    float n0 = __shfl_down_sync(0xffffffffu, b[0], 1);
+    float n1 = __shfl_down_sync(0xffffffffu, b[1], 1);
+    if (lane == 31) { n0 = 0.f; n1 = 0.f; }
+    const float eb = row[blank];
+    float e[NSL / 2];
+#pragma unroll
+    for (int q = 0; q < NSL / 2; ++q) e[q] = row[eidx[q]];
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) {
+        const float p1 = (j + 1 < NSL) ? b[j + 1] : n0;
+        if (j & 1) {
+            const float p2 = (j + 2 < NSL) ? b[j + 2] : n1;
+            u[j] = fmaf(mb[j >> 1], p2, b[j] + p1);
+        } else {
+            u[j] = b[j] + p1;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) b[j] = u[j] * ((j & 1) ? e[j >> 1] : eb);
+}
+
+// sum_s v[s] -> TS; returns the sum before scaling (0 / non-finite / tiny => caller flags the utterance)
+template <int NSL>
+__device__ __forceinline__ float renorm(float (&v)[NSL]) {
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) s += v[j];
+    s = warp_sum(s);
+    const float inv = __fdividef(TS, s);
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) v[j] *= inv;
+    return s;
+}
+
+template <int NSL>
+__global__ void __launch_bounds__(256, 1)
+ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, int Lcap, int vec8) {
+    constexpr int NL = NSL / 2;
+    constexpr int SLOTS = Geo<NSL>::SLOTS;
+    constexpr int RS = Geo<NSL>::RS;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.x * (blockDim.x >> 5) + warp;
+    if (b >= p.B) return;
+
+    extern __shared__ __align__(16) float smem_f[];
+    const FastSmem lay = fast_smem_layout(NSL, CP, Lcap);
+    float* base = smem_f + (size_t)warp * lay.total_floats;
+    float* chunk = base;                                         // [KF][RS]  alpha~ rows, then occupancies
+    float* rows = base + lay.rows_off;                           // [2][KF][CP] exp(lp) rows, row[C..CP) = 0
+    float* occ = base + lay.occ_off;                             // [KF][CP]
+    int* meta = reinterpret_cast<int*>(base + lay.meta_off);     // [Lcap] class-sorted label positions
+    float* zinv = base + lay.zinv_off;                           // [KF]
+    int* lab = reinterpret_cast<int*>(base + lay.lab_off);       // [Lcap]
+
+    const int C = p.C, blank = p.blank, T = p.T;
+    const long long Tb64 = p.in_len[b], L64 = p.tgt_len[b];
+    const bool want_grad = p.grad != nullptr;
+    // anything unusual goes to the log-space kernel, which also owns the error reporting
+    if (Tb64 <= 0 || Tb64 > T || L64 < 0 || L64 > p.Lmax || 2 * L64 + 1 > SLOTS) {
+        if (lane == 0) p.flags[b] = 1;
+        return;
+    }
+    const int Tb = (int)Tb64, L = (int)L64, S = 2 * L + 1;
+    const int64_t* tg = p.tgt_stride ? p.targets + (int64_t)b * p.tgt_stride : p.targets + p.tgt_offsets[b];
+    int flag = 0;
+    for (int i = lane; i < L; i += 32) {
+        const long long v = tg[i];
+        if (v < 0 || v >= C || v == blank) flag = 1;
+        lab[i] = (int)v;
+    }
+    flag = __any_sync(0xffffffffu, flag);
+    if (flag) {
+        if (lane == 0) p.flags[b] = 1;
+        return;
+    }
+    __syncwarp();
+
+    // per-lane constants: emission index and skip masks of my NL label states
+    int eidx[NL];
+    float ma[NL], mb[NL];
+#pragma unroll
+    for (int q = 0; q < NL; ++q) {
+        const int i = lane * NL + q;
+        const bool in = i < L;
+        const int c = in ? lab[i] : C;                          // row[C] == 0
+        eidx[q] = c;
+        ma[q] = (in && i > 0 && lab[i - 1] != c) ? 1.f : 0.f;
+        mb[q] = (in && i + 1 < L && lab[i + 1] != c) ? 1.f : 0.f;
+    }
+
+    const float* lp_b = p.lp + (size_t)b * p.stride_b;
+    const size_t gstride = (size_t)p.B * C;
+    float* gr = want_grad ? p.grad + (size_t)b * C : nullptr;
+    const float g = (p.grad_out ? p.grad_out[b] : 1.f) * p.gscalar;
+    const int nch = (Tb + KF - 1) / KF;
+
+    auto issue_rows = [&](int j, int buf) {
+        const int t0 = j * KF, n = min(KF, Tb - t0);
+        float* dst = rows + buf * KF * CP;
+        for (int r = 0; r < n; ++r) {
+            const float* src = lp_b + (size_t)(t0 + r) * p.stride_t;
+            if (vec8) {
+                for (int c2 = lane; 2 * c2 < C; c2 += 32) cp_async8(dst + r * CP + 2 * c2, src + 2 * c2);
+            } else {
+                for (int c = lane; c < C; c += 32) cp_async4(dst + r * CP + c, src + c);
+            }
+        }
+        cp_async_commit();
+    };
+    auto finish_rows = [&](int j, int buf) {            // lp -> p = exp(lp), zero the pad slots
+        const int n = min(KF, Tb - j * KF);
+        float* dst = rows + buf * KF * CP;
+        for (int r = 0; r < n; ++r)
+            for (int c = lane; c < CP; c += 32) {
+                const float v = dst[r * CP + c];
+                dst[r * CP + c] = c < C ? __expf(v) : 0.f;
+            }
+        __syncwarp();
+    };
+
+    // ------------------------------------------------------------------------------------------ forward sweep
+    float a[NSL];
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) a[j] = 0.f;
+    if (lane == 0) a[0] = TS;                           // virtual alpha_{-1}: one step of the recursion gives alpha_0
+    double lsum = -(double)LOG_TS;                      // alpha = a * exp(lsum)
+    float* ck = ckpt_ws + (size_t)b * n_ckpt * SLOTS;
+
+    issue_rows(0, 0);
+    // rows t >= T_b of the gradient are zero (torch semantics); overlaps with the first loads
+    if (want_grad)
+        for (int t = Tb; t < T; ++t)
+            for (int c = lane; c < C; c += 32) gr[(size_t)t * gstride + c] = 0.f;
+
+    for (int j = 0; j < nch; ++j) {
+        if (j + 1 < nch) { issue_rows(j + 1, (j + 1) & 1); cp_async_wait<1>(); }
+        else cp_async_wait<0>();
+        __syncwarp();
+        finish_rows(j, j & 1);
+        if (want_grad && j > 0) row_store<NSL>(ck + (size_t)j * SLOTS, lane, a);   // alpha~ entering chunk j
+        const float* rb = rows + (j & 1) * KF * CP;
+        const int n = min(KF, Tb - j * KF);
+#pragma unroll 4
+        for (int r = 0; r < n; ++r) {
+            alpha_step<NSL>(a, rb + r * CP, blank, eidx, ma, lane);
+            if ((r & RENORM_MASK) == RENORM_MASK) {
+                const float s = renorm<NSL>(a);
+                lsum += (double)(logf(s) - LOG_TS);
+                if (!(s > TINY) || s > 1e37f) flag = 1;
+            }
+        }
+    }
+    {
+        float v = 0.f;
+#pragma unroll
+        for (int j = 0; j < NSL; ++j) {
+            const int s = lane * NSL + j;
+            if (s == S - 1 || s == S - 2) v += a[j];
+        }
+        v = warp_sum(v);
+        if (!(v > 1e-30f) || v > 1e37f) flag = 1;
+        if (lane == 0 && !flag) {
+            p.nll[b] = (float)(-((double)logf(v) + lsum));
+            if (p.status) p.status[b] = MDD_ST_OK;
+        }
+    }
+    if (flag || !want_grad) {
+        if (lane == 0) p.flags[b] = flag;
+        return;
+    }
+
+    // ------------------------------------------------------------------------------------------ class-sorted list
+    // meta[k] = pos | cls << 9 | end << 16 | start << 17, sorted by class (positions ascending inside a class).
+    int hsplit;
+    {
+        int cnt[4] = {0, 0, 0, 0};
+        for (int i = 0; i < L; ++i) {
+            const int v = lab[i];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) cnt[k] += (v == lane + 32 * k);
+        }
+        int start[4], basek = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            int inc = cnt[k];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            start[k] = basek + inc - cnt[k];
+            basek += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        int best = 0x7fffffff;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int c = lane + 32 * k;
+            if (cnt[k] > 0) {
+                int w = start[k];
+                for (int i = 0; i < L; ++i)
+                    if (lab[i] == c) {
+                        meta[w] = i | (c << 9) | ((w == start[k] + cnt[k] - 1) ? (1 << 16) : 0) | ((w == start[k]) ? (1 << 17) : 0);
+                        ++w;
+                    }
+                const int d = abs(2 * start[k] - L);
+                best = min(best, d * 1024 + start[k]);
+            }
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, d));
+        hsplit = (best == 0x7fffffff) ? 0 : (best & 1023);
+        __syncwarp();
+    }
+
+    // ------------------------------------------------------------------------------------------ backward sweep
+    float bt[NSL];
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) bt[j] = (lane * NSL + j == S - 1) ? TS : 0.f;     // virtual beta_T
+    const int f = lane & 15, h = lane >> 4;
+
+    for (int j = nch - 1; j >= 0; --j) {
+        const int t0 = j * KF, n = min(KF, Tb - t0);
+        const int buf = j & 1;
+        if (j < nch - 1) {                              // the last chunk is still staged (and exponentiated)
+            cp_async_wait<0>();
+            __syncwarp();
+            finish_rows(j, buf);
+        }
+        if (j > 0) issue_rows(j - 1, (j - 1) & 1);      // prefetch the next (earlier) chunk
+        const float* rb = rows + buf * KF * CP;
+
+        // recompute alpha~ for the chunk from its checkpoint
+        if (j == 0) {
+#pragma unroll
+            for (int q = 0; q < NSL; ++q) a[q] = 0.f;
+            if (lane == 0) a[0] = TS;
+        } else {
+            row_load<NSL>(ck + (size_t)j * SLOTS, lane, a);
+        }
+#pragma unroll 4
+        for (int r = 0; r < n; ++r) {
+            alpha_step<NSL>(a, rb + r * CP, blank, eidx, ma, lane);
+            if ((r & RENORM_MASK) == RENORM_MASK) renorm<NSL>(a);
+            row_store<NSL>(chunk + r * RS, lane, a);
+        }
+        __syncwarp();
+
+        // beta, per-state occupancies alpha~_t(s) * u_t(s) (labels -> slots [0, 32*NL), blank partials -> [32*NL, +32))
+        for (int r = n - 1; r >= 0; --r) {
+            float u[NSL], al[NSL];
+            beta_step<NSL>(bt, u, rb + r * CP, blank, eidx, mb, lane);
+            float* cr = chunk + r * RS;
+            row_load<NSL>(cr, lane, al);
+            float bp = 0.f, pl[NL];
+#pragma unroll
+            for (int q = 0; q < NL; ++q) {
+                bp = fmaf(al[2 * q], u[2 * q], bp);
+                pl[q] = al[2 * q + 1] * u[2 * q + 1];
+            }
+            __syncwarp();                               // every lane has read its alpha~ before the row is reused
+            if constexpr (NL == 1) cr[lane] = pl[0];
+            else if constexpr (NL == 2) *reinterpret_cast<float2*>(cr + 2 * lane) = make_float2(pl[0], pl[1]);
+            else {
+#pragma unroll
+                for (int q4 = 0; q4 < NL / 4; ++q4)
+                    *reinterpret_cast<float4*>(cr + NL * lane + 4 * q4) = make_float4(pl[4 * q4], pl[4 * q4 + 1], pl[4 * q4 + 2], pl[4 * q4 + 3]);
+            }
+            cr[32 * NL + lane] = bp;
+            if ((r & RENORM_MASK) == 0) {
+                const float s = renorm<NSL>(bt);
+                if (!(s > TINY) || s > 1e37f) flag = 1;
+            }
+        }
+        // clear the occupancy table of the chunk
+        for (int i = lane; i < n * CP; i += 32) occ[i] = 0.f;
+        __syncwarp();
+
+        // chunk-batched class reduction: lane = (frame f, half h of the class-sorted list)
+        {
+            const int kb = h ? hsplit : 0, ke = h ? L : hsplit;
+            const int niter = max(hsplit, L - hsplit);
+            const float* pr = chunk + f * RS;
+            const bool live = f < n;
+            float acc = 0.f, tot = 0.f;
+            for (int it = 0; it < niter; ++it) {
+                const int k = kb + it;
+                if (live && k < ke) {
+                    const int m = meta[k];
+                    const float v = pr[m & 511];
+                    acc = (m & (1 << 17)) ? v : acc + v;
+                    tot += v;
+                    if (m & (1 << 16)) occ[f * CP + ((m >> 9) & 127)] = acc;
+                }
+            }
+            float bs = 0.f;
+            if (live) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) bs += pr[32 * NL + 16 * h + i];
+            }
+            const float bs_o = __shfl_xor_sync(0xffffffffu, bs, 16);
+            const float tot_o = __shfl_xor_sync(0xffffffffu, tot, 16);
+            if (h == 0 && live) {
+                const float blank_occ = bs + bs_o;
+                const float Z = (tot + tot_o) + blank_occ;
+                occ[f * CP + blank] = blank_occ;
+                zinv[f] = __fdividef(1.f, Z);
+                if (!(Z > 1e-30f) || Z > 1e37f) flag = 1;
+            }
+        }
+        __syncwarp();
+
+        // grad rows of the chunk: (softmax prob - occupancy / Z) * g
+        for (int r = 0; r < n; ++r) {
+            const float zi = zinv[r];
+            float* grow = gr + (size_t)(t0 + r) * gstride;
+            for (int c = lane; c < C; c += 32) grow[c] = (rb[r * CP + c] - occ[r * CP + c] * zi) * g;
+        }
+        __syncwarp();
+    }
+    flag = __any_sync(0xffffffffu, flag);
+    if (lane == 0) p.flags[b] = flag;
+}
+
+int pick_nsl(int Lmax) {
+    const int S = 2 * Lmax + 1;
+    if (S <= 64) return 2;
+    if (S <= 128) return 4;
+    if (S <= 256) return 8;
+    if (S <= 512) return 16;
+    return 0;
+}
+inline int cp_of(int C) { return (C + 2) & ~1; }
+inline int lcap_of(int Lmax) { return ((Lmax > 0 ? Lmax : 1) + 3) & ~3; }
+
+template <int NSL>
+int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
+    const int CP = cp_of(p.C), Lcap = lcap_of(p.Lmax);
+    const FastSmem lay = fast_smem_layout(NSL, CP, Lcap);
+    const size_t per_warp = (size_t)lay.total_floats * 4;
+    int warps = (int)((220 * 1024) / per_warp);
+    if (warps > 8) warps = 8;
+    if (warps < 1) return MDD_E_UNSUPPORTED;
+    // small batches: spread the utterances over the SMs instead of packing 8 per CTA
+    const int spread = (p.B + kNumSM - 1) / kNumSM;
+    if (warps > spread) warps = spread > 0 ? spread : 1;
+    const size_t smem = per_warp * warps;
+    static size_t configured = 0;
+    if (smem > configured) {
+        if (cudaFuncSetAttribute(ctc_fast_kernel<NSL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024) != cudaSuccess) {
+            cudaGetLastError();
+            return MDD_E_CUDA;
+        }
+        configured = 220 * 1024;
+    }
+    const int n_ckpt = (p.T + KF - 1) / KF + 1;
+    const int vec8 = (p.C % 2 == 0) && (p.stride_t % 2 == 0) && (p.stride_b % 2 == 0) && ((uintptr_t)p.lp % 8 == 0);
+    const int grid = (p.B + warps - 1) / warps;
+    ctc_fast_kernel<NSL><<<grid, warps * 32, smem, st>>>(p, ws, n_ckpt, CP, Lcap, vec8);
+    MDD_CHECK_LAUNCH();
+    return MDD_OK;
+}
+
+}  // namespace
+
+bool ctc_fast_supported(int C, int Lmax) { return C <= MDD_MAX_CLASSES && pick_nsl(Lmax) != 0; }
+
+size_t ctc_fast_ws_bytes(int T, int B, int Lmax) {
+    const int nsl = pick_nsl(Lmax);
+    if (!nsl) return 0;
+    const size_t n_ckpt = (size_t)(T + KF - 1) / KF + 1;
+    return (size_t)B * n_ckpt * 32 * nsl * 4;
+}
+
+int launch_ctc_fast(CtcParams p, void* ws, cudaStream_t st) {
+    float* w = reinterpret_cast<float*>(ws);
+    switch (pick_nsl(p.Lmax)) {
+        case 2: return launch_nsl<2>(p, w, st);
+        case 4: return launch_nsl<4>(p, w, st);
+        case 8: return launch_nsl<8>(p, w, st);
+        case 16: return launch_nsl<16>(p, w, st);
+        default: return MDD_E_UNSUPPORTED;
+    }
+}
+
 }  // namespace mdd

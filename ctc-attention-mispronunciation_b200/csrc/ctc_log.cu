@@ -265,8 +265,12 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
             __syncthreads();
             // per-class LSE_{s in c}(alpha~ + beta~) - lp[c]   (alpha and beta both carry the emission at t)
             if (tid < 32) {
-                const float lcab = block_lse_blank(ab, S, nullptr, tid);
-                if (tid == 0) s_lc[blank] = lcab - rw[blank];
+                float lcab = block_lse_blank(ab, S, nullptr, tid);
+                if (tid == 0) {
+                    // targets equal to the blank index (legal for torch): their label states also count for class blank
+                    for (int n = cls_start[blank]; n < cls_start[blank + 1]; ++n) lcab = lse2_acc(lcab, ab[2 * cls_list[n] + 1]);
+                    s_lc[blank] = lcab - rw[blank];
+                }
             } else if (tid < 32 + C) {
                 const int c = tid - 32;
                 if (c != blank) {
