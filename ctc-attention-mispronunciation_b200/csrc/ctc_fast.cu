@@ -6,11 +6,16 @@
 // Why not log space: a per-state log-sum-exp lattice needs ~7 MUFU ops per state-frame (S = 2L+1 = 241 states at
 // L = 120), which bounds the kernel at ~10 % of the HBM roofline on the SFU pipe alone.  Here the
 // emissions are exponentiated once per (t,c) and alpha/beta are propagated as plain products and sums (FADD/FMUL/
-// FFMA), renormalised every 4 frames to a fixed sum (2^32) with the log of the scale accumulated in fp64 for the
-// loss.  The occupancy is self-normalised per frame (Z_t = sum_s alpha_t(s) u_t(s)), so no scale bookkeeping enters the
-// gradient.  Utterances whose scales under/overflow (or that are infeasible, empty or malformed) set flags[b] and are
-// redone by the log-space kernel (ctc_log.cu) in the same stream: results never depend on this path being exact
-// for pathological inputs.
+// FFMA) in a block-floating-point format: every lane carries one integer exponent for the NSL states it owns and
+// renormalises its mantissas every 4 frames from its own maximum (no warp reduction).  A plain "scale the whole column"
+// normalisation is not enough: with T >> L the alpha mass runs ahead to the last states and the beta mass back to the
+// first ones, so at the states the posterior lives on both are > 2^126 below their column sums and fp32 loses them.
+// Per-lane exponents give each 4-label stretch of the lattice its own range; neighbouring lanes exchange boundary
+// states with a 2^(e_nb - e_me) factor that only changes at renormalisation time.  The loss is read off the final
+// mantissa and exponent (no per-frame log), and the occupancy is self-normalised per frame
+// (Z_t = sum_s alpha_t(s) u_t(s)), so no scale bookkeeping enters the gradient.  Utterances that are infeasible, empty,
+// malformed or whose ranges still do not fit set flags[b] and are redone by the log-space kernel (ctc_log.cu) in the
+// same stream: results never depend on this path being exact for pathological inputs.
 //
 // Mapping: one warp per utterance, NSL consecutive lattice states per lane held in registers; the s-1 / s-2
 // neighbours across lanes come from one __shfl_up (alpha) or two __shfl_down (beta): no block barrier anywhere in the
@@ -30,10 +35,8 @@ namespace mdd {
 namespace {
 
 constexpr int KF = 16;                 // frames per chunk
-constexpr int RENORM_MASK = 3;         // renormalise after frames with (t & 3) == 3
-constexpr float TS = 4294967296.f;     // 2^32: renormalisation target for sum_s alpha~ (centres the fp32 range)
-constexpr float LOG_TS = 22.180709777918249f;
-constexpr float TINY = 1e-18f;         // scale sums below this hand the utterance to the log-space kernel
+constexpr int RENORM_MASK = 3;         // renormalise before frames with (t & 3) == 0 (alpha) / == 3 (beta)
+constexpr int E_EMPTY = -(1 << 20);    // exponent of a lane whose states are all zero
 
 __device__ __forceinline__ void cp_async4(void* dst, const void* src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
@@ -49,6 +52,10 @@ template <int NSL>
 struct Geo {
     static constexpr int NL = NSL / 2;            // label states per lane (odd j)
     static constexpr int SLOTS = 32 * NSL;        // lattice slots per utterance
+    // A lane's exponent is kept within 2^GAP of the lane it receives from.  Between two renormalisations (4 frames)
+    // mass can cross ceil(8/NSL)+1 lane boundaries, each multiplying the mantissa by up to 2^GAP, so GAP * crossings
+    // (+7 bits of growth) must stay below the fp32 exponent range.
+    static constexpr int GAP = NSL == 2 ? 20 : NSL == 4 ? 36 : 56;
     static constexpr int RS = SLOTS + 4;          // shared-memory row stride (floats): +4 keeps 16 B alignment and
                                                   // spreads the 16 frame rows over banks for the class walk
 };
@@ -79,7 +86,7 @@ __device__ __forceinline__ void row_load(const float* row, int lane, float (&a)[
 }
 
 struct FastSmem {          // per-warp carve-up (floats / ints), computed on the host and in the kernel identically
-    int rows_off, occ_off, meta_off, zinv_off, lab_off, total_floats;
+    int rows_off, occ_off, meta_off, zinv_off, lab_off, eat_off, total_floats;
 };
 __host__ __device__ inline FastSmem fast_smem_layout(int NSL, int CP, int Lcap) {
     FastSmem s;
@@ -89,21 +96,22 @@ __host__ __device__ inline FastSmem fast_smem_layout(int NSL, int CP, int Lcap) 
     s.meta_off = o; o += Lcap;            // class-sorted position list
     s.zinv_off = o; o += KF;
     s.lab_off = o;  o += Lcap;            // labels
+    s.eat_off = o;  o += 4 * 32;          // alpha exponents of the chunk's four renormalisation groups
     s.total_floats = (o + 3) & ~3;
     return s;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// One lattice step.  Lane l owns states s = NSL*l + j; even j = blank, odd j = label q = (j-1)/2.
+// One lattice step.  Lane l owns states s = NSL*l + j; even j = blank, odd j = label q = (j-1)/2.  Values are
+// mantissas relative to the lane's exponent; sc_in = 2^(e_neighbour - e_me) rescales what crosses the lane boundary.
 //   alpha: new[s] = (a[s] + a[s-1] + ma * a[s-2]) * e[s]        (ma = skip allowed into label s)
 //   beta : u[s]   =  b[s] + b[s+1] + mb * b[s+2];  new b[s] = u[s] * e[s]   (u = beta without the emission at t)
 // Label slots past the end of the target read a zero emission (row[C] = 0), which also keeps every later slot at 0.
 // ---------------------------------------------------------------------------------------------------------------
 template <int NSL>
-__device__ __forceinline__ void alpha_step(float (&a)[NSL], const float* __restrict__ row, int blank,
-                                           const int (&eidx)[NSL / 2], const float (&ma)[NSL / 2], int lane) {
-    float p = __shfl_up_sync(0xffffffffu, a[NSL - 1], 1);     // state NSL*l - 1 (a label state)
-    if (lane == 0) p = 0.f;
+__device__ __forceinline__ void alpha_step(float (&a)[NSL], float sc_in, const float* __restrict__ row, int blank,
+                                           const int (&eidx)[NSL / 2], const float (&ma)[NSL / 2]) {
+    const float p = __shfl_up_sync(0xffffffffu, a[NSL - 1], 1) * sc_in;     // state NSL*l - 1 (sc_in == 0 on lane 0)
     const float eb = row[blank];
     float e[NSL / 2];
 #pragma unroll
@@ -124,11 +132,10 @@ __device__ __forceinline__ void alpha_step(float (&a)[NSL], const float* __restr
 }
 
 template <int NSL>
-__device__ __forceinline__ void beta_step(float (&b)[NSL], float (&u)[NSL], const float* __restrict__ row, int blank,
-                                          const int (&eidx)[NSL / 2], const float (&mb)[NSL / 2], int lane) {
-    float n0 = __shfl_down_sync(0xffffffffu, b[0], 1);
-    float n1 = __shfl_down_sync(0xffffffffu, b[1], 1);
-    if (lane == 31) { n0 = 0.f; n1 = 0.f; }
+__device__ __forceinline__ void beta_step(float (&b)[NSL], float (&u)[NSL], float sc_in, const float* __restrict__ row,
+                                          int blank, const int (&eidx)[NSL / 2], const float (&mb)[NSL / 2]) {
+    const float n0 = __shfl_down_sync(0xffffffffu, b[0], 1) * sc_in;        // sc_in == 0 on lane 31
+    const float n1 = __shfl_down_sync(0xffffffffu, b[1], 1) * sc_in;
     const float eb = row[blank];
     float e[NSL / 2];
 #pragma unroll
@@ -147,17 +154,40 @@ __device__ __forceinline__ void beta_step(float (&b)[NSL], float (&u)[NSL], cons
     for (int j = 0; j < NSL; ++j) b[j] = u[j] * ((j & 1) ? e[j >> 1] : eb);
 }
 
-// sum_s v[s] -> TS; returns the sum before scaling (0 / non-finite / tiny => caller flags the utterance)
-template <int NSL>
-__device__ __forceinline__ float renorm(float (&v)[NSL]) {
-    float s = 0.f;
+__device__ __forceinline__ float pow2i(int x) {            // 2^x, 0 below the normal range
+    return x < -126 ? 0.f : __int_as_float((127 + min(x, 127)) << 23);
+}
+
+// Per-lane renormalisation.  v = mantissas, e = the lane's exponent.  The lane's maximum is brought to [1,2); a lane
+// is never allowed more than 2^GAP below the lane it receives from (FWD: lane-1, else lane+1) so that the boundary
+// factor sc_in = 2^(e_nb - e_me) stays finite; empty lanes inherit their exponent from that side.
+// Returns false if every lane is empty (no alignment mass left) or real content had to be squashed by > 2^100.
+template <int NSL, bool FWD>
+__device__ __forceinline__ bool renorm_lane(float (&v)[NSL], int& e, float& sc_in, int lane) {
+    float m = v[0];
 #pragma unroll
-    for (int j = 0; j < NSL; ++j) s += v[j];
-    s = warp_sum(s);
-    const float inv = __fdividef(TS, s);
+    for (int j = 1; j < NSL; ++j) m = fmaxf(m, v[j]);
+    const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;
+    const bool some = m >= 1.17549435e-38f && m < 3.0e38f;       // normal, finite (NaN fails both)
+    const int e_own = some ? e + k : E_EMPTY;
+    constexpr int GAP = Geo<NSL>::GAP;
+    const int pos = FWD ? lane : 31 - lane;
+    int t = e_own + GAP * pos;
 #pragma unroll
-    for (int j = 0; j < NSL; ++j) v[j] *= inv;
-    return s;
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = FWD ? __shfl_up_sync(0xffffffffu, t, d) : __shfl_down_sync(0xffffffffu, t, d);
+        if (pos >= d) t = max(t, o);
+    }
+    const int e_new = t - GAP * pos;
+    const float f = pow2i(e - e_new);
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) v[j] *= f;
+    e = e_new;
+    const int e_nb = FWD ? __shfl_up_sync(0xffffffffu, e_new, 1) : __shfl_down_sync(0xffffffffu, e_new, 1);
+    sc_in = (pos == 0) ? 0.f : pow2i(e_nb - e_new);
+    const bool bad = (m != m) || m >= 3.0e38f || (some && e_new - e_own > 100);
+    const bool alive = __any_sync(0xffffffffu, some);
+    return alive && !__any_sync(0xffffffffu, bad);
 }
 
 template <int NSL>
@@ -179,6 +209,7 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     int* meta = reinterpret_cast<int*>(base + lay.meta_off);     // [Lcap] class-sorted label positions
     float* zinv = base + lay.zinv_off;                           // [KF]
     int* lab = reinterpret_cast<int*>(base + lay.lab_off);       // [Lcap]
+    int* eat = reinterpret_cast<int*>(base + lay.eat_off);       // [4][32]
 
     const int C = p.C, blank = p.blank, T = p.T;
     const long long Tb64 = p.in_len[b], L64 = p.tgt_len[b];
@@ -247,12 +278,14 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     };
 
     // ------------------------------------------------------------------------------------------ forward sweep
+    constexpr int CKS = SLOTS + 32;                     // checkpoint row: mantissas + one exponent per lane
     float a[NSL];
 #pragma unroll
     for (int j = 0; j < NSL; ++j) a[j] = 0.f;
-    if (lane == 0) a[0] = TS;                           // virtual alpha_{-1}: one step of the recursion gives alpha_0
-    double lsum = -(double)LOG_TS;                      // alpha = a * exp(lsum)
-    float* ck = ckpt_ws + (size_t)b * n_ckpt * SLOTS;
+    if (lane == 0) a[0] = 1.f;                          // virtual alpha_{-1}: one step of the recursion gives alpha_0
+    int ea = 0;                                         // alpha(s) = a[j] * 2^ea
+    float sca = 0.f;                                    // 2^(ea[lane-1] - ea[lane])
+    float* ck = ckpt_ws + (size_t)b * n_ckpt * CKS;
 
     issue_rows(0, 0);
     // rows t >= T_b of the gradient are zero (torch semantics); overlaps with the first loads
@@ -265,30 +298,34 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
         else cp_async_wait<0>();
         __syncwarp();
         finish_rows(j, j & 1);
-        if (want_grad && j > 0) row_store<NSL>(ck + (size_t)j * SLOTS, lane, a);   // alpha~ entering chunk j
+        if (want_grad && j > 0) {                       // alpha entering chunk j (before its first renormalisation)
+            row_store<NSL>(ck + (size_t)j * CKS, lane, a);
+            ck[(size_t)j * CKS + SLOTS + lane] = __int_as_float(ea);
+        }
         const float* rb = rows + (j & 1) * KF * CP;
         const int n = min(KF, Tb - j * KF);
 #pragma unroll 4
         for (int r = 0; r < n; ++r) {
-            alpha_step<NSL>(a, rb + r * CP, blank, eidx, ma, lane);
-            if ((r & RENORM_MASK) == RENORM_MASK) {
-                const float s = renorm<NSL>(a);
-                lsum += (double)(logf(s) - LOG_TS);
-                if (!(s > TINY) || s > 1e37f) flag = 1;
+            if ((r & RENORM_MASK) == 0) {
+                if (!renorm_lane<NSL, true>(a, ea, sca, lane) && !flag) flag = 2 | ((j * KF + r) << 8);
             }
+            alpha_step<NSL>(a, sca, rb + r * CP, blank, eidx, ma);
         }
     }
-    {
+    {   // P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2), possibly in two lanes with different exponents
         float v = 0.f;
 #pragma unroll
         for (int j = 0; j < NSL; ++j) {
             const int s = lane * NSL + j;
             if (s == S - 1 || s == S - 2) v += a[j];
         }
-        v = warp_sum(v);
-        if (!(v > 1e-30f) || v > 1e37f) flag = 1;
+        int em = (v > 0.f) ? ea : E_EMPTY;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) em = max(em, __shfl_xor_sync(0xffffffffu, em, d));
+        v = warp_sum(v * pow2i(ea - em));
+        if ((em == E_EMPTY || !(v > 1e-30f) || v > 1e37f) && !flag) flag = 3;
         if (lane == 0 && !flag) {
-            p.nll[b] = (float)(-((double)logf(v) + lsum));
+            p.nll[b] = (float)(-((double)logf(v) + (double)em * 0.69314718055994530942));
             if (p.status) p.status[b] = MDD_ST_OK;
         }
     }
@@ -343,7 +380,9 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     // ------------------------------------------------------------------------------------------ backward sweep
     float bt[NSL];
 #pragma unroll
-    for (int j = 0; j < NSL; ++j) bt[j] = (lane * NSL + j == S - 1) ? TS : 0.f;     // virtual beta_T
+    for (int j = 0; j < NSL; ++j) bt[j] = (lane * NSL + j == S - 1) ? 1.f : 0.f;     // virtual beta_T
+    int eb = 0;
+    float scb = 0.f;
     const int f = lane & 15, h = lane >> 4;
 
     for (int j = nch - 1; j >= 0; --j) {
@@ -357,35 +396,51 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
         if (j > 0) issue_rows(j - 1, (j - 1) & 1);      // prefetch the next (earlier) chunk
         const float* rb = rows + buf * KF * CP;
 
-        // recompute alpha~ for the chunk from its checkpoint
+        // recompute alpha for the chunk from its checkpoint (bitwise the same operations as the forward sweep)
         if (j == 0) {
 #pragma unroll
             for (int q = 0; q < NSL; ++q) a[q] = 0.f;
-            if (lane == 0) a[0] = TS;
+            if (lane == 0) a[0] = 1.f;
+            ea = 0;
         } else {
-            row_load<NSL>(ck + (size_t)j * SLOTS, lane, a);
+            row_load<NSL>(ck + (size_t)j * CKS, lane, a);
+            ea = __float_as_int(ck[(size_t)j * CKS + SLOTS + lane]);
         }
 #pragma unroll 4
         for (int r = 0; r < n; ++r) {
-            alpha_step<NSL>(a, rb + r * CP, blank, eidx, ma, lane);
-            if ((r & RENORM_MASK) == RENORM_MASK) renorm<NSL>(a);
+            if ((r & RENORM_MASK) == 0) {
+                renorm_lane<NSL, true>(a, ea, sca, lane);
+                eat[(r >> 2) * 32 + lane] = ea;
+            }
+            alpha_step<NSL>(a, sca, rb + r * CP, blank, eidx, ma);
             row_store<NSL>(chunk + r * RS, lane, a);
         }
         __syncwarp();
 
-        // beta, per-state occupancies alpha~_t(s) * u_t(s) (labels -> slots [0, 32*NL), blank partials -> [32*NL, +32))
+        // beta, per-state occupancies alpha_t(s) * u_t(s) on a per-frame common scale
+        // (labels -> slots [0, 32*NL), blank partial sums -> [32*NL, +32))
+        float scp = 0.f;                                // 2^(ea + eb - max over lanes)
         for (int r = n - 1; r >= 0; --r) {
+            if (r == n - 1 || (r & RENORM_MASK) == RENORM_MASK) {
+                if (!renorm_lane<NSL, false>(bt, eb, scb, lane) && !flag) flag = 4 | ((t0 + r) << 8);
+                const int E = eat[(r >> 2) * 32 + lane] + eb;
+                int Em = E;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) Em = max(Em, __shfl_xor_sync(0xffffffffu, Em, d));
+                scp = pow2i(E - Em);
+            }
             float u[NSL], al[NSL];
-            beta_step<NSL>(bt, u, rb + r * CP, blank, eidx, mb, lane);
+            beta_step<NSL>(bt, u, scb, rb + r * CP, blank, eidx, mb);
             float* cr = chunk + r * RS;
             row_load<NSL>(cr, lane, al);
             float bp = 0.f, pl[NL];
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
                 bp = fmaf(al[2 * q], u[2 * q], bp);
-                pl[q] = al[2 * q + 1] * u[2 * q + 1];
+                pl[q] = al[2 * q + 1] * u[2 * q + 1] * scp;
             }
-            __syncwarp();                               // every lane has read its alpha~ before the row is reused
+            bp *= scp;
+            __syncwarp();                               // every lane has read its alpha before the row is reused
             if constexpr (NL == 1) cr[lane] = pl[0];
             else if constexpr (NL == 2) *reinterpret_cast<float2*>(cr + 2 * lane) = make_float2(pl[0], pl[1]);
             else {
@@ -394,10 +449,6 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
                     *reinterpret_cast<float4*>(cr + NL * lane + 4 * q4) = make_float4(pl[4 * q4], pl[4 * q4 + 1], pl[4 * q4 + 2], pl[4 * q4 + 3]);
             }
             cr[32 * NL + lane] = bp;
-            if ((r & RENORM_MASK) == 0) {
-                const float s = renorm<NSL>(bt);
-                if (!(s > TINY) || s > 1e37f) flag = 1;
-            }
         }
         // clear the occupancy table of the chunk
         for (int i = lane; i < n * CP; i += 32) occ[i] = 0.f;
@@ -432,7 +483,7 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
                 const float Z = (tot + tot_o) + blank_occ;
                 occ[f * CP + blank] = blank_occ;
                 zinv[f] = __fdividef(1.f, Z);
-                if (!(Z > 1e-30f) || Z > 1e37f) flag = 1;
+                if ((!(Z > 1e-30f) || Z > 1e37f) && !flag) flag = 5 | ((t0 + f) << 8);
             }
         }
         __syncwarp();
@@ -445,8 +496,12 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
         }
         __syncwarp();
     }
-    flag = __any_sync(0xffffffffu, flag);
-    if (lane == 0) p.flags[b] = flag;
+    {
+        int fl = flag;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) fl = max(fl, __shfl_xor_sync(0xffffffffu, fl, d));
+        if (lane == 0) p.flags[b] = fl;     // 0 = done here; otherwise reason | frame << 8 (diagnostic), redone in log space
+    }
 }
 
 int pick_nsl(int Lmax) {
@@ -496,7 +551,7 @@ size_t ctc_fast_ws_bytes(int T, int B, int Lmax) {
     const int nsl = pick_nsl(Lmax);
     if (!nsl) return 0;
     const size_t n_ckpt = (size_t)(T + KF - 1) / KF + 1;
-    return (size_t)B * n_ckpt * 32 * nsl * 4;
+    return (size_t)B * n_ckpt * (32 * nsl + 32) * 4;     // mantissas + per-lane exponents
 }
 
 int launch_ctc_fast(CtcParams p, void* ws, cudaStream_t st) {
