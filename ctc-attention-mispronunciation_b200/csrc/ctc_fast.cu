@@ -22,31 +22,23 @@
 // recursion.  Eight warps (adjacent utterances, so their 168 B rows of one frame form one contiguous run in HBM)
 // share a CTA only to share the SM.
 //
-// Memory: the lattice never goes to HBM.  Forward sweep: log-prob rows are staged 16 frames at a time with cp.async
-// (double buffered), alpha enters each 16-frame chunk as a checkpoint row written to the workspace (S*4/16 B per
-// frame).  Backward sweep, chunks from the end: reload the chunk's rows (the last chunk is still in shared memory),
-// recompute alpha for 16 frames into shared memory, run beta; each frame's per-state occupancies overwrite the alpha
-// row, and a chunk-batched, deterministic class reduction (a class-sorted position list built once per utterance;
-// lanes = 16 frames x 2 halves of the list) produces grad = (p - occupancy / Z) * g for 16 rows at once.
+// Memory: the lattice never goes to HBM.  Forward sweep: log-prob rows are read KF frames ahead straight into
+// registers (one 8-byte load per lane per row), exponentiated and parked in shared memory when the chunk starts;
+// alpha enters each chunk as a checkpoint row written to the workspace ((S+32)*4/KF B per frame).  Backward sweep,
+// chunks from the end: reload the chunk's rows (the last chunk is still in shared memory), recompute alpha for KF
+// frames into shared memory, run beta; each frame's per-state occupancies overwrite the alpha row in class-sorted
+// order, and a chunk-batched, deterministic class reduction (lanes = KF frames x 32/KF stretches of the sorted
+// list) produces grad = (p - occupancy / Z) * g for KF rows at once.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "ctc_params.cuh"
 
 namespace mdd {
 namespace {
 
-constexpr int KF = 16;                 // frames per chunk
 constexpr int RENORM_MASK = 3;         // renormalise before frames with (t & 3) == 0 (alpha) / == 3 (beta)
 constexpr int E_EMPTY = -(1 << 20);    // exponent of a lane whose states are all zero
-
-__device__ __forceinline__ void cp_async4(void* dst, const void* src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <int NSL>
 struct Geo {
@@ -57,7 +49,7 @@ struct Geo {
     // (+7 bits of growth) must stay below the fp32 exponent range.
     static constexpr int GAP = NSL == 2 ? 20 : NSL == 4 ? 36 : 56;
     static constexpr int RS = SLOTS + 4;          // shared-memory row stride (floats): +4 keeps 16 B alignment and
-                                                  // spreads the 16 frame rows over banks for the class walk
+                                                  // spreads the frame rows over banks for the class walk
 };
 
 // alpha~ row <-> registers.  Layout: float4 group g of lane l at (g*128 + 4*l): conflict-free 128-bit accesses.
@@ -88,15 +80,15 @@ __device__ __forceinline__ void row_load(const float* row, int lane, float (&a)[
 struct FastSmem {          // per-warp carve-up (floats / ints), computed on the host and in the kernel identically
     int rows_off, occ_off, meta_off, zinv_off, lab_off, eat_off, total_floats;
 };
-__host__ __device__ inline FastSmem fast_smem_layout(int NSL, int CP, int Lcap) {
+__host__ __device__ inline FastSmem fast_smem_layout(int NSL, int KF, int CP, int Lcap) {
     FastSmem s;
-    int o = KF * (32 * NSL + 4);          // alpha~ chunk
-    s.rows_off = o; o += 2 * KF * CP;     // two staged row chunks
+    int o = KF * (32 * NSL + 4);          // alpha chunk, then occupancies
+    s.rows_off = o; o += KF * CP;         // exp(lp) rows of the current chunk
     s.occ_off = o;  o += KF * CP;         // per-frame class occupancies
-    s.meta_off = o; o += Lcap;            // class-sorted position list
+    s.meta_off = o; o += Lcap;            // class of every class-sorted label slot (+ segment flags)
     s.zinv_off = o; o += KF;
     s.lab_off = o;  o += Lcap;            // labels
-    s.eat_off = o;  o += 4 * 32;          // alpha exponents of the chunk's four renormalisation groups
+    s.eat_off = o;  o += (KF / 4) * 32;   // alpha exponents of the chunk's renormalisation groups
     s.total_floats = (o + 3) & ~3;
     return s;
 }
@@ -190,26 +182,70 @@ __device__ __forceinline__ bool renorm_lane(float (&v)[NSL], int& e, float& sc_i
     return alive && !__any_sync(0xffffffffu, bad);
 }
 
-template <int NSL>
-__global__ void __launch_bounds__(256, 1)
-ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, int Lcap, int vec8) {
+
+// Two floats per lane per row: VEC -> columns (2*lane, 2*lane+1) as one 8-byte access, else columns (lane, lane+32).
+template <bool VEC>
+__device__ __forceinline__ float2 ld_row2(const float* __restrict__ src, int lane, int C) {
+    if constexpr (VEC) {
+        return (2 * lane < C) ? __ldcs(reinterpret_cast<const float2*>(src) + lane) : make_float2(0.f, 0.f);
+    } else {
+        float2 v;
+        v.x = lane < C ? __ldcs(src + lane) : 0.f;
+        v.y = lane + 32 < C ? __ldcs(src + lane + 32) : 0.f;
+        return v;
+    }
+}
+template <bool VEC>
+__device__ __forceinline__ void st_row2_smem(float* __restrict__ dst, int lane, int C, float2 v) {
+    if constexpr (VEC) {
+        if (2 * lane < C) reinterpret_cast<float2*>(dst)[lane] = v;
+    } else {
+        if (lane < C) dst[lane] = v.x;
+        if (lane + 32 < C) dst[lane + 32] = v.y;
+    }
+}
+template <bool VEC>
+__device__ __forceinline__ float2 ld_row2_smem(const float* __restrict__ src, int lane, int C) {
+    if constexpr (VEC) {
+        return (2 * lane < C) ? reinterpret_cast<const float2*>(src)[lane] : make_float2(0.f, 0.f);
+    } else {
+        return make_float2(lane < C ? src[lane] : 0.f, lane + 32 < C ? src[lane + 32] : 0.f);
+    }
+}
+template <bool VEC>
+__device__ __forceinline__ void st_row2_gmem(float* __restrict__ dst, int lane, int C, float2 v) {
+    if constexpr (VEC) {
+        if (2 * lane < C) __stcs(reinterpret_cast<float2*>(dst) + lane, v);
+    } else {
+        if (lane < C) __stcs(dst + lane, v.x);
+        if (lane + 32 < C) __stcs(dst + lane + 32, v.y);
+    }
+}
+
+template <int NSL, int KF, bool VEC>
+__global__ void __launch_bounds__(KF == 16 ? 256 : 512, 1)
+ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, int Lcap) {
     constexpr int NL = NSL / 2;
     constexpr int SLOTS = Geo<NSL>::SLOTS;
     constexpr int RS = Geo<NSL>::RS;
+    constexpr int CKS = SLOTS + 32;                     // checkpoint row: mantissas + one exponent per lane
+    constexpr int NPART = 32 / KF;                      // stretches of the class-sorted list walked in parallel
+    constexpr int DUMP = 32 * NL + 32;                  // row slot that swallows the products of unused label slots
+    static_assert(DUMP < RS, "row too short");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.x * (blockDim.x >> 5) + warp;
     if (b >= p.B) return;
 
     extern __shared__ __align__(16) float smem_f[];
-    const FastSmem lay = fast_smem_layout(NSL, CP, Lcap);
+    const FastSmem lay = fast_smem_layout(NSL, KF, CP, Lcap);
     float* base = smem_f + (size_t)warp * lay.total_floats;
-    float* chunk = base;                                         // [KF][RS]  alpha~ rows, then occupancies
-    float* rows = base + lay.rows_off;                           // [2][KF][CP] exp(lp) rows, row[C..CP) = 0
+    float* chunk = base;                                         // [KF][RS]  alpha rows, then occupancies
+    float* rows = base + lay.rows_off;                           // [KF][CP] exp(lp) rows, row[C..CP) = 0
     float* occ = base + lay.occ_off;                             // [KF][CP]
-    int* meta = reinterpret_cast<int*>(base + lay.meta_off);     // [Lcap] class-sorted label positions
+    int* meta = reinterpret_cast<int*>(base + lay.meta_off);     // [Lcap] cls | end << 8 | start << 9 per sorted slot
     float* zinv = base + lay.zinv_off;                           // [KF]
     int* lab = reinterpret_cast<int*>(base + lay.lab_off);       // [Lcap]
-    int* eat = reinterpret_cast<int*>(base + lay.eat_off);       // [4][32]
+    int* eat = reinterpret_cast<int*>(base + lay.eat_off);       // [KF/4][32]
 
     const int C = p.C, blank = p.blank, T = p.T;
     const long long Tb64 = p.in_len[b], L64 = p.tgt_len[b];
@@ -232,6 +268,11 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
         if (lane == 0) p.flags[b] = 1;
         return;
     }
+    // zero pads of the staged rows (never overwritten) and the occupancy table (absent classes stay 0)
+    if (lane < KF) {
+        for (int c = C; c < CP; ++c) rows[lane * CP + c] = 0.f;
+    }
+    for (int i = lane; i < KF * CP; i += 32) occ[i] = 0.f;
     __syncwarp();
 
     // per-lane constants: emission index and skip masks of my NL label states
@@ -253,32 +294,21 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     const float g = (p.grad_out ? p.grad_out[b] : 1.f) * p.gscalar;
     const int nch = (Tb + KF - 1) / KF;
 
-    auto issue_rows = [&](int j, int buf) {
+    float2 pre[KF];                                     // the next chunk's rows, in flight
+    auto load_rows = [&](int j) {
         const int t0 = j * KF, n = min(KF, Tb - t0);
-        float* dst = rows + buf * KF * CP;
-        for (int r = 0; r < n; ++r) {
-            const float* src = lp_b + (size_t)(t0 + r) * p.stride_t;
-            if (vec8) {
-                for (int c2 = lane; 2 * c2 < C; c2 += 32) cp_async8(dst + r * CP + 2 * c2, src + 2 * c2);
-            } else {
-                for (int c = lane; c < C; c += 32) cp_async4(dst + r * CP + c, src + c);
-            }
-        }
-        cp_async_commit();
+        const float* src = lp_b + (size_t)t0 * p.stride_t;
+#pragma unroll
+        for (int r = 0; r < KF; ++r)
+            if (r < n) pre[r] = ld_row2<VEC>(src + (size_t)r * p.stride_t, lane, C);
     };
-    auto finish_rows = [&](int j, int buf) {            // lp -> p = exp(lp), zero the pad slots
-        const int n = min(KF, Tb - j * KF);
-        float* dst = rows + buf * KF * CP;
-        for (int r = 0; r < n; ++r)
-            for (int c = lane; c < CP; c += 32) {
-                const float v = dst[r * CP + c];
-                dst[r * CP + c] = c < C ? __expf(v) : 0.f;
-            }
-        __syncwarp();
+    auto commit_rows = [&](int n) {                     // p = exp(lp) into shared memory
+#pragma unroll
+        for (int r = 0; r < KF; ++r)
+            if (r < n) st_row2_smem<VEC>(rows + r * CP, lane, C, make_float2(__expf(pre[r].x), __expf(pre[r].y)));
     };
 
     // ------------------------------------------------------------------------------------------ forward sweep
-    constexpr int CKS = SLOTS + 32;                     // checkpoint row: mantissas + one exponent per lane
     float a[NSL];
 #pragma unroll
     for (int j = 0; j < NSL; ++j) a[j] = 0.f;
@@ -287,29 +317,27 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     float sca = 0.f;                                    // 2^(ea[lane-1] - ea[lane])
     float* ck = ckpt_ws + (size_t)b * n_ckpt * CKS;
 
-    issue_rows(0, 0);
+    load_rows(0);
     // rows t >= T_b of the gradient are zero (torch semantics); overlaps with the first loads
     if (want_grad)
-        for (int t = Tb; t < T; ++t)
-            for (int c = lane; c < C; c += 32) gr[(size_t)t * gstride + c] = 0.f;
+        for (int t = Tb; t < T; ++t) st_row2_gmem<VEC>(gr + (size_t)t * gstride, lane, C, make_float2(0.f, 0.f));
 
     for (int j = 0; j < nch; ++j) {
-        if (j + 1 < nch) { issue_rows(j + 1, (j + 1) & 1); cp_async_wait<1>(); }
-        else cp_async_wait<0>();
+        const int n = min(KF, Tb - j * KF);
         __syncwarp();
-        finish_rows(j, j & 1);
+        commit_rows(n);
+        __syncwarp();
+        if (j + 1 < nch) load_rows(j + 1);
         if (want_grad && j > 0) {                       // alpha entering chunk j (before its first renormalisation)
             row_store<NSL>(ck + (size_t)j * CKS, lane, a);
             ck[(size_t)j * CKS + SLOTS + lane] = __int_as_float(ea);
         }
-        const float* rb = rows + (j & 1) * KF * CP;
-        const int n = min(KF, Tb - j * KF);
 #pragma unroll 4
         for (int r = 0; r < n; ++r) {
             if ((r & RENORM_MASK) == 0) {
                 if (!renorm_lane<NSL, true>(a, ea, sca, lane) && !flag) flag = 2 | ((j * KF + r) << 8);
             }
-            alpha_step<NSL>(a, sca, rb + r * CP, blank, eidx, ma);
+            alpha_step<NSL>(a, sca, rows + r * CP, blank, eidx, ma);
         }
     }
     {   // P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2), possibly in two lanes with different exponents
@@ -334,19 +362,22 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
         return;
     }
 
-    // ------------------------------------------------------------------------------------------ class-sorted list
-    // meta[k] = pos | cls << 9 | end << 16 | start << 17, sorted by class (positions ascending inside a class).
-    int hsplit;
+    // ------------------------------------------------------------------------------------------ class-sorted layout
+    // Label i gets slot perm(i) of a list sorted by class (positions ascending inside a class); meta[slot] holds the
+    // class and the segment flags.  split[] cuts the list at class boundaries into NPART stretches of similar length.
+    int perm[NL];
+    int split[NPART + 1];
     {
-        int cnt[4] = {0, 0, 0, 0};
+        int* scratch = reinterpret_cast<int*>(chunk);   // label -> slot, read back into registers below
+        int cnt[2] = {0, 0};
         for (int i = 0; i < L; ++i) {
             const int v = lab[i];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) cnt[k] += (v == lane + 32 * k);
+            cnt[0] += (v == lane);
+            cnt[1] += (v == lane + 32);
         }
-        int start[4], basek = 0;
+        int start[2], basek = 0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 2; ++k) {
             int inc = cnt[k];
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
@@ -356,24 +387,40 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
             start[k] = basek + inc - cnt[k];
             basek += __shfl_sync(0xffffffffu, inc, 31);
         }
-        int best = 0x7fffffff;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 2; ++k) {
             const int c = lane + 32 * k;
             if (cnt[k] > 0) {
                 int w = start[k];
                 for (int i = 0; i < L; ++i)
                     if (lab[i] == c) {
-                        meta[w] = i | (c << 9) | ((w == start[k] + cnt[k] - 1) ? (1 << 16) : 0) | ((w == start[k]) ? (1 << 17) : 0);
+                        meta[w] = c | ((w == start[k] + cnt[k] - 1) ? (1 << 8) : 0) | ((w == start[k]) ? (1 << 9) : 0);
+                        scratch[i] = w;
                         ++w;
                     }
-                const int d = abs(2 * start[k] - L);
-                best = min(best, d * 1024 + start[k]);
             }
         }
+        split[0] = 0;
+        split[NPART] = L;
 #pragma unroll
-        for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, d));
-        hsplit = (best == 0x7fffffff) ? 0 : (best & 1023);
+        for (int part = 1; part < NPART; ++part) {
+            const int want = (L * part) / NPART;
+            int best = 0x7fffffff;
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+                if (cnt[k] > 0) best = min(best, abs(start[k] - want) * 1024 + start[k]);
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, d));
+            split[part] = (best == 0x7fffffff) ? 0 : (best & 1023);
+        }
+#pragma unroll
+        for (int part = 1; part < NPART; ++part) split[part] = max(split[part], split[part - 1]);
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < NL; ++q) {
+            const int i = lane * NL + q;
+            perm[q] = i < L ? scratch[i] : DUMP;
+        }
         __syncwarp();
     }
 
@@ -383,18 +430,22 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     for (int j = 0; j < NSL; ++j) bt[j] = (lane * NSL + j == S - 1) ? 1.f : 0.f;     // virtual beta_T
     int eb = 0;
     float scb = 0.f;
-    const int f = lane & 15, h = lane >> 4;
+    const int f = lane & (KF - 1), h = lane / KF;
+    int kb = 0, ke = 0, niter = 0;
+#pragma unroll
+    for (int part = 0; part < NPART; ++part) {
+        if (h == part) { kb = split[part]; ke = split[part + 1]; }
+        niter = max(niter, split[part + 1] - split[part]);
+    }
 
     for (int j = nch - 1; j >= 0; --j) {
         const int t0 = j * KF, n = min(KF, Tb - t0);
-        const int buf = j & 1;
         if (j < nch - 1) {                              // the last chunk is still staged (and exponentiated)
-            cp_async_wait<0>();
             __syncwarp();
-            finish_rows(j, buf);
+            commit_rows(n);
+            __syncwarp();
         }
-        if (j > 0) issue_rows(j - 1, (j - 1) & 1);      // prefetch the next (earlier) chunk
-        const float* rb = rows + buf * KF * CP;
+        if (j > 0) load_rows(j - 1);                    // prefetch the next (earlier) chunk
 
         // recompute alpha for the chunk from its checkpoint (bitwise the same operations as the forward sweep)
         if (j == 0) {
@@ -412,13 +463,13 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
                 renorm_lane<NSL, true>(a, ea, sca, lane);
                 eat[(r >> 2) * 32 + lane] = ea;
             }
-            alpha_step<NSL>(a, sca, rb + r * CP, blank, eidx, ma);
+            alpha_step<NSL>(a, sca, rows + r * CP, blank, eidx, ma);
             row_store<NSL>(chunk + r * RS, lane, a);
         }
         __syncwarp();
 
         // beta, per-state occupancies alpha_t(s) * u_t(s) on a per-frame common scale
-        // (labels -> slots [0, 32*NL), blank partial sums -> [32*NL, +32))
+        // (labels -> class-sorted slots [0, L), blank partial sums -> [32*NL, +32))
         float scp = 0.f;                                // 2^(ea + eb - max over lanes)
         for (int r = n - 1; r >= 0; --r) {
             if (r == n - 1 || (r & RENORM_MASK) == RENORM_MASK) {
@@ -430,7 +481,7 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
                 scp = pow2i(E - Em);
             }
             float u[NSL], al[NSL];
-            beta_step<NSL>(bt, u, scb, rb + r * CP, blank, eidx, mb);
+            beta_step<NSL>(bt, u, scb, rows + r * CP, blank, eidx, mb);
             float* cr = chunk + r * RS;
             row_load<NSL>(cr, lane, al);
             float bp = 0.f, pl[NL];
@@ -441,58 +492,54 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
             }
             bp *= scp;
             __syncwarp();                               // every lane has read its alpha before the row is reused
-            if constexpr (NL == 1) cr[lane] = pl[0];
-            else if constexpr (NL == 2) *reinterpret_cast<float2*>(cr + 2 * lane) = make_float2(pl[0], pl[1]);
-            else {
 #pragma unroll
-                for (int q4 = 0; q4 < NL / 4; ++q4)
-                    *reinterpret_cast<float4*>(cr + NL * lane + 4 * q4) = make_float4(pl[4 * q4], pl[4 * q4 + 1], pl[4 * q4 + 2], pl[4 * q4 + 3]);
-            }
+            for (int q = 0; q < NL; ++q) cr[perm[q]] = pl[q];
             cr[32 * NL + lane] = bp;
         }
-        // clear the occupancy table of the chunk
-        for (int i = lane; i < n * CP; i += 32) occ[i] = 0.f;
         __syncwarp();
 
-        // chunk-batched class reduction: lane = (frame f, half h of the class-sorted list)
+        // chunk-batched class reduction: lane = (frame f, stretch h of the class-sorted list)
         {
-            const int kb = h ? hsplit : 0, ke = h ? L : hsplit;
-            const int niter = max(hsplit, L - hsplit);
             const float* pr = chunk + f * RS;
+            float* of = occ + f * CP;
             const bool live = f < n;
+            const int k1 = live ? ke : kb;
             float acc = 0.f, tot = 0.f;
-            for (int it = 0; it < niter; ++it) {
-                const int k = kb + it;
-                if (live && k < ke) {
-                    const int m = meta[k];
-                    const float v = pr[m & 511];
-                    acc = (m & (1 << 17)) ? v : acc + v;
-                    tot += v;
-                    if (m & (1 << 16)) occ[f * CP + ((m >> 9) & 127)] = acc;
-                }
+            for (int k = kb; k < k1; ++k) {
+                const int m = meta[k];
+                const float v = pr[k];
+                acc = (m & (1 << 9)) ? v : acc + v;
+                tot += v;
+                if (m & (1 << 8)) of[m & 0xff] = acc;
             }
             float bs = 0.f;
             if (live) {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) bs += pr[32 * NL + 16 * h + i];
+                for (int i = 0; i < KF; ++i) bs += pr[32 * NL + KF * h + i];
             }
-            const float bs_o = __shfl_xor_sync(0xffffffffu, bs, 16);
-            const float tot_o = __shfl_xor_sync(0xffffffffu, tot, 16);
+#pragma unroll
+            for (int d = KF; d < 32; d <<= 1) {
+                bs += __shfl_xor_sync(0xffffffffu, bs, d);
+                tot += __shfl_xor_sync(0xffffffffu, tot, d);
+            }
             if (h == 0 && live) {
-                const float blank_occ = bs + bs_o;
-                const float Z = (tot + tot_o) + blank_occ;
-                occ[f * CP + blank] = blank_occ;
+                const float Z = tot + bs;
+                of[blank] = bs;
                 zinv[f] = __fdividef(1.f, Z);
                 if ((!(Z > 1e-30f) || Z > 1e37f) && !flag) flag = 5 | ((t0 + f) << 8);
             }
+            (void)niter;
         }
         __syncwarp();
 
         // grad rows of the chunk: (softmax prob - occupancy / Z) * g
+#pragma unroll 4
         for (int r = 0; r < n; ++r) {
-            const float zi = zinv[r];
-            float* grow = gr + (size_t)(t0 + r) * gstride;
-            for (int c = lane; c < C; c += 32) grow[c] = (rb[r * CP + c] - occ[r * CP + c] * zi) * g;
+            const float zi = zinv[r] ;
+            const float2 pv = ld_row2_smem<VEC>(rows + r * CP, lane, C);
+            const float2 ov = ld_row2_smem<VEC>(occ + r * CP, lane, C);
+            st_row2_gmem<VEC>(gr + (size_t)(t0 + r) * gstride, lane, C,
+                              make_float2((pv.x - ov.x * zi) * g, (pv.y - ov.y * zi) * g));
         }
         __syncwarp();
     }
@@ -515,43 +562,60 @@ int pick_nsl(int Lmax) {
 inline int cp_of(int C) { return (C + 2) & ~1; }
 inline int lcap_of(int Lmax) { return ((Lmax > 0 ? Lmax : 1) + 3) & ~3; }
 
-template <int NSL>
-int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
+int fast_kf() {                         // frames per chunk: 8 (more warps per SM) or 16 (half the checkpoint traffic)
+    static int kf = 0;
+    if (!kf) {
+        const char* e = getenv("MDD_CTC_FAST_KF");
+        kf = (e && atoi(e) == 16) ? 16 : 8;
+    }
+    return kf;
+}
+
+template <int NSL, int KF, bool VEC>
+int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
     const int CP = cp_of(p.C), Lcap = lcap_of(p.Lmax);
-    const FastSmem lay = fast_smem_layout(NSL, CP, Lcap);
+    const FastSmem lay = fast_smem_layout(NSL, KF, CP, Lcap);
     const size_t per_warp = (size_t)lay.total_floats * 4;
-    int warps = (int)((220 * 1024) / per_warp);
-    if (warps > 8) warps = 8;
+    constexpr int kMaxWarps = KF == 16 ? 8 : 16;
+    int warps = (int)((224 * 1024) / per_warp);
+    if (warps > kMaxWarps) warps = kMaxWarps;
     if (warps < 1) return MDD_E_UNSUPPORTED;
-    // small batches: spread the utterances over the SMs instead of packing 8 per CTA
+    // small batches: spread the utterances over the SMs instead of packing them into few CTAs
     const int spread = (p.B + kNumSM - 1) / kNumSM;
     if (warps > spread) warps = spread > 0 ? spread : 1;
     const size_t smem = per_warp * warps;
-    static size_t configured = 0;
-    if (smem > configured) {
-        if (cudaFuncSetAttribute(ctc_fast_kernel<NSL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024) != cudaSuccess) {
+    static bool configured = false;
+    if (!configured) {
+        if (cudaFuncSetAttribute(ctc_fast_kernel<NSL, KF, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024) != cudaSuccess) {
             cudaGetLastError();
             return MDD_E_CUDA;
         }
-        configured = 220 * 1024;
+        configured = true;
     }
     const int n_ckpt = (p.T + KF - 1) / KF + 1;
-    const int vec8 = (p.C % 2 == 0) && (p.stride_t % 2 == 0) && (p.stride_b % 2 == 0) && ((uintptr_t)p.lp % 8 == 0);
     const int grid = (p.B + warps - 1) / warps;
-    ctc_fast_kernel<NSL><<<grid, warps * 32, smem, st>>>(p, ws, n_ckpt, CP, Lcap, vec8);
+    ctc_fast_kernel<NSL, KF, VEC><<<grid, warps * 32, smem, st>>>(p, ws, n_ckpt, CP, Lcap);
     MDD_CHECK_LAUNCH();
     return MDD_OK;
 }
 
+template <int NSL>
+int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
+    const bool vec = (p.C % 2 == 0) && (p.stride_t % 2 == 0) && (p.stride_b % 2 == 0) && ((uintptr_t)p.lp % 8 == 0) &&
+                     (!p.grad || (uintptr_t)p.grad % 8 == 0);
+    if (fast_kf() == 16) return vec ? launch_cfg<NSL, 16, true>(p, ws, st) : launch_cfg<NSL, 16, false>(p, ws, st);
+    return vec ? launch_cfg<NSL, 8, true>(p, ws, st) : launch_cfg<NSL, 8, false>(p, ws, st);
+}
+
 }  // namespace
 
-bool ctc_fast_supported(int C, int Lmax) { return C <= MDD_MAX_CLASSES && pick_nsl(Lmax) != 0; }
+bool ctc_fast_supported(int C, int Lmax) { return C <= 64 && pick_nsl(Lmax) != 0; }
 
 size_t ctc_fast_ws_bytes(int T, int B, int Lmax) {
     const int nsl = pick_nsl(Lmax);
     if (!nsl) return 0;
-    const size_t n_ckpt = (size_t)(T + KF - 1) / KF + 1;
-    return (size_t)B * n_ckpt * (32 * nsl + 32) * 4;     // mantissas + per-lane exponents
+    const size_t n_ckpt = (size_t)(T + 7) / 8 + 1;           // sized for the smaller chunk (KF = 8)
+    return (size_t)B * n_ckpt * (32 * nsl + 32) * 4;         // mantissas + per-lane exponents
 }
 
 int launch_ctc_fast(CtcParams p, void* ws, cudaStream_t st) {
