@@ -78,15 +78,13 @@ __device__ __forceinline__ void row_load(const float* row, int lane, float (&a)[
 }
 
 struct FastSmem {          // per-warp carve-up (floats / ints), computed on the host and in the kernel identically
-    int rows_off, occ_off, meta_off, zinv_off, lab_off, eat_off, total_floats;
+    int rows_off, ctab_off, lab_off, eat_off, total_floats;
 };
 __host__ __device__ inline FastSmem fast_smem_layout(int NSL, int KF, int CP, int Lcap) {
     FastSmem s;
-    int o = KF * (32 * NSL + 4);          // alpha chunk, then occupancies
+    int o = KF * (32 * NSL + 4);          // alpha chunk, then occupancy prefix sums
     s.rows_off = o; o += KF * CP;         // exp(lp) rows of the current chunk
-    s.occ_off = o;  o += KF * CP;         // per-frame class occupancies
-    s.meta_off = o; o += Lcap;            // class of every class-sorted label slot (+ segment flags)
-    s.zinv_off = o; o += KF;
+    s.ctab_off = o; o += 128;             // per class: first slot, count in the class-sorted order
     s.lab_off = o;  o += Lcap;            // labels
     s.eat_off = o;  o += (KF / 4) * 32;   // alpha exponents of the chunk's renormalisation groups
     s.total_floats = (o + 3) & ~3;
@@ -183,43 +181,47 @@ __device__ __forceinline__ bool renorm_lane(float (&v)[NSL], int& e, float& sc_i
 }
 
 
-// Two floats per lane per row: VEC -> columns (2*lane, 2*lane+1) as one 8-byte access, else columns (lane, lane+32).
+// Two floats per lane per row.  VEC: columns (2*lane, 2*lane+1) as one 8-byte access, else columns (lane, lane+32).
+// Loads are unconditional (lanes past the row re-read a clamped column) so that a chunk's loads issue back to back.
+struct Cols {
+    int c0, c1;         // my two columns (class ids)
+    bool v0, v1;        // inside the row?
+    int l0, l1;         // clamped columns for the unconditional loads
+};
 template <bool VEC>
-__device__ __forceinline__ float2 ld_row2(const float* __restrict__ src, int lane, int C) {
-    if constexpr (VEC) {
-        return (2 * lane < C) ? __ldcs(reinterpret_cast<const float2*>(src) + lane) : make_float2(0.f, 0.f);
-    } else {
-        float2 v;
-        v.x = lane < C ? __ldcs(src + lane) : 0.f;
-        v.y = lane + 32 < C ? __ldcs(src + lane + 32) : 0.f;
-        return v;
-    }
+__device__ __forceinline__ Cols make_cols(int lane, int C) {
+    Cols k;
+    if constexpr (VEC) { k.c0 = 2 * lane; k.c1 = 2 * lane + 1; k.v0 = k.v1 = (2 * lane < C); }
+    else { k.c0 = lane; k.c1 = lane + 32; k.v0 = lane < C; k.v1 = lane + 32 < C; }
+    k.l0 = k.v0 ? k.c0 : 0;
+    k.l1 = k.v1 ? k.c1 : 0;
+    return k;
 }
 template <bool VEC>
-__device__ __forceinline__ void st_row2_smem(float* __restrict__ dst, int lane, int C, float2 v) {
-    if constexpr (VEC) {
-        if (2 * lane < C) reinterpret_cast<float2*>(dst)[lane] = v;
-    } else {
-        if (lane < C) dst[lane] = v.x;
-        if (lane + 32 < C) dst[lane + 32] = v.y;
-    }
+__device__ __forceinline__ float2 ld_row2(const float* __restrict__ src, const Cols& k) {
+    if constexpr (VEC) return __ldcs(reinterpret_cast<const float2*>(src + k.l0));
+    else return make_float2(__ldcs(src + k.l0), __ldcs(src + k.l1));
 }
 template <bool VEC>
-__device__ __forceinline__ float2 ld_row2_smem(const float* __restrict__ src, int lane, int C) {
-    if constexpr (VEC) {
-        return (2 * lane < C) ? reinterpret_cast<const float2*>(src)[lane] : make_float2(0.f, 0.f);
-    } else {
-        return make_float2(lane < C ? src[lane] : 0.f, lane + 32 < C ? src[lane + 32] : 0.f);
-    }
+__device__ __forceinline__ void st_row2_smem(float* __restrict__ dst, const Cols& k, float2 v) {
+    if constexpr (VEC) { if (k.v0) *reinterpret_cast<float2*>(dst + k.c0) = v; }
+    else { if (k.v0) dst[k.c0] = v.x; if (k.v1) dst[k.c1] = v.y; }
 }
 template <bool VEC>
-__device__ __forceinline__ void st_row2_gmem(float* __restrict__ dst, int lane, int C, float2 v) {
-    if constexpr (VEC) {
-        if (2 * lane < C) __stcs(reinterpret_cast<float2*>(dst) + lane, v);
-    } else {
-        if (lane < C) __stcs(dst + lane, v.x);
-        if (lane + 32 < C) __stcs(dst + lane + 32, v.y);
-    }
+__device__ __forceinline__ float2 ld_row2_smem(const float* __restrict__ src, const Cols& k) {
+    if constexpr (VEC) return *reinterpret_cast<const float2*>(src + k.l0);
+    else return make_float2(src[k.l0], src[k.l1]);
+}
+template <bool VEC>
+__device__ __forceinline__ void st_row2_gmem(float* __restrict__ dst, const Cols& k, float2 v) {
+    if constexpr (VEC) { if (k.v0) __stcs(reinterpret_cast<float2*>(dst + k.c0), v); }
+    else { if (k.v0) __stcs(dst + k.c0, v.x); if (k.v1) __stcs(dst + k.c1, v.y); }
+}
+// exp(x) = 2^(x * log2 e) on the SFU; results below 2^-126 flush to 0 (such rows end in the log-space kernel anyway)
+__device__ __forceinline__ float fast_exp(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+    return y;
 }
 
 template <int NSL, int KF, bool VEC>
@@ -230,8 +232,12 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     constexpr int RS = Geo<NSL>::RS;
     constexpr int CKS = SLOTS + 32;                     // checkpoint row: mantissas + one exponent per lane
     constexpr int NPART = 32 / KF;                      // stretches of the class-sorted list walked in parallel
-    constexpr int DUMP = 32 * NL + 32;                  // row slot that swallows the products of unused label slots
-    static_assert(DUMP < RS, "row too short");
+    // the four spare slots at the end of every chunk row
+    constexpr int DUMP = SLOTS;                         // swallows the products of unused label slots
+    constexpr int ZERO = SLOTS + 1;                     // always 0
+    constexpr int BLK = SLOTS + 2;                      // blank-class occupancy of the frame
+    constexpr int ZINV = SLOTS + 3;                     // 1 / Z_t
+    static_assert(RS == SLOTS + 4, "row layout");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.x * (blockDim.x >> 5) + warp;
     if (b >= p.B) return;
@@ -239,11 +245,9 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     extern __shared__ __align__(16) float smem_f[];
     const FastSmem lay = fast_smem_layout(NSL, KF, CP, Lcap);
     float* base = smem_f + (size_t)warp * lay.total_floats;
-    float* chunk = base;                                         // [KF][RS]  alpha rows, then occupancies
+    float* chunk = base;                                         // [KF][RS]  alpha rows, then occupancy prefix sums
     float* rows = base + lay.rows_off;                           // [KF][CP] exp(lp) rows, row[C..CP) = 0
-    float* occ = base + lay.occ_off;                             // [KF][CP]
-    int* meta = reinterpret_cast<int*>(base + lay.meta_off);     // [Lcap] cls | end << 8 | start << 9 per sorted slot
-    float* zinv = base + lay.zinv_off;                           // [KF]
+    int* ctab = reinterpret_cast<int*>(base + lay.ctab_off);     // [64] first sorted slot, [64] count per class
     int* lab = reinterpret_cast<int*>(base + lay.lab_off);       // [Lcap]
     int* eat = reinterpret_cast<int*>(base + lay.eat_off);       // [KF/4][32]
 
@@ -268,11 +272,12 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
         if (lane == 0) p.flags[b] = 1;
         return;
     }
-    // zero pads of the staged rows (never overwritten) and the occupancy table (absent classes stay 0)
+    // zero pads of the staged rows and the ZERO slot of the chunk rows (never overwritten)
     if (lane < KF) {
         for (int c = C; c < CP; ++c) rows[lane * CP + c] = 0.f;
+        chunk[lane * RS + ZERO] = 0.f;
     }
-    for (int i = lane; i < KF * CP; i += 32) occ[i] = 0.f;
+    const Cols cols = make_cols<VEC>(lane, C);
     __syncwarp();
 
     // per-lane constants: emission index and skip masks of my NL label states
@@ -295,17 +300,16 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     const int nch = (Tb + KF - 1) / KF;
 
     float2 pre[KF];                                     // the next chunk's rows, in flight
-    auto load_rows = [&](int j) {
+    auto load_rows = [&](int j) {                       // rows past the end of a partial chunk re-read its last row
         const int t0 = j * KF, n = min(KF, Tb - t0);
         const float* src = lp_b + (size_t)t0 * p.stride_t;
 #pragma unroll
-        for (int r = 0; r < KF; ++r)
-            if (r < n) pre[r] = ld_row2<VEC>(src + (size_t)r * p.stride_t, lane, C);
+        for (int r = 0; r < KF; ++r) pre[r] = ld_row2<VEC>(src + (size_t)min(r, n - 1) * p.stride_t, cols);
     };
-    auto commit_rows = [&](int n) {                     // p = exp(lp) into shared memory
+    auto commit_rows = [&]() {                          // p = exp(lp) into shared memory
 #pragma unroll
         for (int r = 0; r < KF; ++r)
-            if (r < n) st_row2_smem<VEC>(rows + r * CP, lane, C, make_float2(__expf(pre[r].x), __expf(pre[r].y)));
+            st_row2_smem<VEC>(rows + r * CP, cols, make_float2(fast_exp(pre[r].x), fast_exp(pre[r].y)));
     };
 
     // ------------------------------------------------------------------------------------------ forward sweep
@@ -320,12 +324,12 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     load_rows(0);
     // rows t >= T_b of the gradient are zero (torch semantics); overlaps with the first loads
     if (want_grad)
-        for (int t = Tb; t < T; ++t) st_row2_gmem<VEC>(gr + (size_t)t * gstride, lane, C, make_float2(0.f, 0.f));
+        for (int t = Tb; t < T; ++t) st_row2_gmem<VEC>(gr + (size_t)t * gstride, cols, make_float2(0.f, 0.f));
 
     for (int j = 0; j < nch; ++j) {
         const int n = min(KF, Tb - j * KF);
         __syncwarp();
-        commit_rows(n);
+        commit_rows();
         __syncwarp();
         if (j + 1 < nch) load_rows(j + 1);
         if (want_grad && j > 0) {                       // alpha entering chunk j (before its first renormalisation)
@@ -363,10 +367,12 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     }
 
     // ------------------------------------------------------------------------------------------ class-sorted layout
-    // Label i gets slot perm(i) of a list sorted by class (positions ascending inside a class); meta[slot] holds the
-    // class and the segment flags.  split[] cuts the list at class boundaries into NPART stretches of similar length.
+    // Label i gets slot perm(i) of a list sorted by class (positions ascending inside a class).  split[] cuts the list
+    // at class boundaries into NPART stretches of similar length; each stretch is prefix-summed independently, so the
+    // occupancy of class c is P[oe] - P[os] with os = ZERO when c opens a stretch (absent classes: both ZERO).
     int perm[NL];
     int split[NPART + 1];
+    int oe0, os0, oe1, os1;
     {
         int* scratch = reinterpret_cast<int*>(chunk);   // label -> slot, read back into registers below
         int cnt[2] = {0, 0};
@@ -390,11 +396,12 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
             const int c = lane + 32 * k;
+            ctab[c] = start[k];
+            ctab[64 + c] = cnt[k];
             if (cnt[k] > 0) {
                 int w = start[k];
                 for (int i = 0; i < L; ++i)
                     if (lab[i] == c) {
-                        meta[w] = c | ((w == start[k] + cnt[k] - 1) ? (1 << 8) : 0) | ((w == start[k]) ? (1 << 9) : 0);
                         scratch[i] = w;
                         ++w;
                     }
@@ -421,6 +428,20 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
             const int i = lane * NL + q;
             perm[q] = i < L ? scratch[i] : DUMP;
         }
+        auto occ_slots = [&](int c, bool valid, int& oe, int& os) {
+            oe = ZERO; os = ZERO;
+            if (!valid) return;
+            if (c == blank) { oe = BLK; return; }
+            const int st = ctab[c], n = ctab[64 + c];
+            if (n == 0) return;
+            oe = st + n - 1;
+            bool opens = false;
+#pragma unroll
+            for (int part = 0; part < NPART; ++part) opens |= (st == split[part]);
+            os = opens ? ZERO : st - 1;
+        };
+        occ_slots(cols.c0, cols.v0, oe0, os0);
+        occ_slots(cols.c1, cols.v1, oe1, os1);
         __syncwarp();
     }
 
@@ -431,18 +452,16 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
     int eb = 0;
     float scb = 0.f;
     const int f = lane & (KF - 1), h = lane / KF;
-    int kb = 0, ke = 0, niter = 0;
+    int kb = 0, ke = 0;
 #pragma unroll
-    for (int part = 0; part < NPART; ++part) {
+    for (int part = 0; part < NPART; ++part)
         if (h == part) { kb = split[part]; ke = split[part + 1]; }
-        niter = max(niter, split[part + 1] - split[part]);
-    }
 
     for (int j = nch - 1; j >= 0; --j) {
         const int t0 = j * KF, n = min(KF, Tb - t0);
         if (j < nch - 1) {                              // the last chunk is still staged (and exponentiated)
             __syncwarp();
-            commit_rows(n);
+            commit_rows();
             __syncwarp();
         }
         if (j > 0) load_rows(j - 1);                    // prefetch the next (earlier) chunk
@@ -498,19 +517,15 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
         }
         __syncwarp();
 
-        // chunk-batched class reduction: lane = (frame f, stretch h of the class-sorted list)
+        // chunk-batched class reduction: lane = (frame f, stretch h of the class-sorted list); in-place prefix sums
         {
-            const float* pr = chunk + f * RS;
-            float* of = occ + f * CP;
+            float* pr = chunk + f * RS;
             const bool live = f < n;
             const int k1 = live ? ke : kb;
-            float acc = 0.f, tot = 0.f;
+            float acc = 0.f;
             for (int k = kb; k < k1; ++k) {
-                const int m = meta[k];
-                const float v = pr[k];
-                acc = (m & (1 << 9)) ? v : acc + v;
-                tot += v;
-                if (m & (1 << 8)) of[m & 0xff] = acc;
+                acc += pr[k];
+                pr[k] = acc;
             }
             float bs = 0.f;
             if (live) {
@@ -520,26 +535,26 @@ ctc_fast_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt, int CP, in
 #pragma unroll
             for (int d = KF; d < 32; d <<= 1) {
                 bs += __shfl_xor_sync(0xffffffffu, bs, d);
-                tot += __shfl_xor_sync(0xffffffffu, tot, d);
+                acc += __shfl_xor_sync(0xffffffffu, acc, d);
             }
             if (h == 0 && live) {
-                const float Z = tot + bs;
-                of[blank] = bs;
-                zinv[f] = __fdividef(1.f, Z);
+                const float Z = acc + bs;
+                pr[BLK] = bs;
+                pr[ZINV] = __fdividef(1.f, Z);
                 if ((!(Z > 1e-30f) || Z > 1e37f) && !flag) flag = 5 | ((t0 + f) << 8);
             }
-            (void)niter;
         }
         __syncwarp();
 
         // grad rows of the chunk: (softmax prob - occupancy / Z) * g
 #pragma unroll 4
         for (int r = 0; r < n; ++r) {
-            const float zi = zinv[r] ;
-            const float2 pv = ld_row2_smem<VEC>(rows + r * CP, lane, C);
-            const float2 ov = ld_row2_smem<VEC>(occ + r * CP, lane, C);
-            st_row2_gmem<VEC>(gr + (size_t)(t0 + r) * gstride, lane, C,
-                              make_float2((pv.x - ov.x * zi) * g, (pv.y - ov.y * zi) * g));
+            const float* pr = chunk + r * RS;
+            const float zi = pr[ZINV];
+            const float2 pv = ld_row2_smem<VEC>(rows + r * CP, cols);
+            const float o0 = pr[oe0] - pr[os0], o1 = pr[oe1] - pr[os1];
+            st_row2_gmem<VEC>(gr + (size_t)(t0 + r) * gstride, cols,
+                              make_float2((pv.x - o0 * zi) * g, (pv.y - o1 * zi) * g));
         }
         __syncwarp();
     }
