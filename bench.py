@@ -106,12 +106,28 @@ def measured_peak_gbs():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(name, algo):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the committed ncu --set full
+    capture of this workload (profiles/ncu_traffic.json); None when no capture exists for it."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        return json.load(open(p)).get("%s/algo%d" % (name, algo), {}).get("bytes")
+    except Exception:
+        return None
+
+
 def cpu_reference_arm(name, steps, warmup, slice_b=None):
     """torch CPU ctc_loss fwd+bwd (the reference's implementation of the path) on a bounded slice, all host threads."""
     T, B, C, L, seed = WORKLOADS[name]
     sb = min(B, slice_b or (256 if name == "c3" else B))
     lp, tg, il, tl = make_inputs(name)
     lp, tg, il, tl = lp[:, :sb].contiguous(), tg[:sb], il[:sb], tl[:sb]
+    # all the host threads the process may use (torchrun exports OMP_NUM_THREADS=1, which would hide the cores)
+    try:
+        ncores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        ncores = os.cpu_count() or 1
+    torch.set_num_threads(max(ncores, 1))
     threads = torch.get_num_threads()
     loss_fn = torch.nn.CTCLoss(reduction="sum")
 
@@ -262,7 +278,7 @@ def run_ours(args):
                            "algo": args.algo, "loss": loss_val},
                 "clocks": clk.summary(),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                             "traffic": ncu_traffic(name, args.algo), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                              "kernel_ms": kernel_ms,
                              "note": "CUDA-event time of one mdd_ctc_loss call (main kernel + fallback sweep + loss sum)"},
                 "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
