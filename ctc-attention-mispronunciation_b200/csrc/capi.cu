@@ -33,17 +33,17 @@ CtcWs ctc_ws_layout(int T, int B, int C, int Lmax, int algo) {
     w.off_offsets = o; o = align_up(o + (size_t)B * 8, 256);
     w.off_flags = o;   o = align_up(o + (size_t)B * 4, 256);
     w.off_ckpt = o;
-    const bool fast = algo != 1 && ctc_fast_supported(C, Lmax);
-    if (algo == 1 || !fast || algo == 0) o = align_up(o + ctc_log_ckpt_bytes(T, B, Lmax), 256);
+    const bool fast = algo != 1 && ctc_fast_supported(C, Lmax) && ctc_pair_supported(C, Lmax);
+    if (algo == 1 || !fast || algo == 0 || algo == 3) o = align_up(o + ctc_log_ckpt_bytes(T, B, Lmax), 256);
     w.off_fast = o;
-    if (fast) o = align_up(o + ctc_fast_ws_bytes(T, B, Lmax), 256);
+    if (fast) o = align_up(o + (algo == 3 ? ctc_fast_ws_bytes(T, B, Lmax) : ctc_pair_ws_bytes(T, B, Lmax)), 256);
     w.total = o;
     return w;
 }
 }  // namespace
 
 extern "C" int mdd_ctc_loss_workspace_bytes(int T, int B, int C, int max_target_len, int algo, size_t* bytes) {
-    if (!bytes || T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || algo < 0 || algo > 2)
+    if (!bytes || T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || algo < 0 || algo > 3)
         return MDD_E_ARG;
     *bytes = ctc_ws_layout(T, B, C, max_target_len, algo).total;
     return MDD_OK;
@@ -55,7 +55,7 @@ extern "C" int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t
                             const float* grad_out, float grad_out_scalar, float* nll, float* grad, float* loss_sum,
                             int32_t* status, int algo, void* workspace, size_t workspace_bytes, mdd_stream_t stream) {
     if (T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || blank < 0 || blank >= C || algo < 0 ||
-        algo > 2)
+        algo > 3)
         return MDD_E_ARG;
     if (B == 0) return MDD_OK;
     if ((!log_probs && T > 0) || !input_lengths || !target_lengths || !nll || (!targets && max_target_len > 0))
@@ -79,12 +79,13 @@ extern "C" int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t
         rc = launch_tgt_offsets(target_lengths, B, reinterpret_cast<int64_t*>(ws + w.off_offsets), st);
         if (rc) return rc;
     }
-    const bool fast = algo != 1 && ctc_fast_supported(C, max_target_len) && T > 0;
+    const bool fast = algo != 1 && ctc_fast_supported(C, max_target_len) && ctc_pair_supported(C, max_target_len) && T > 0;
     if (algo == 2 && !fast) return MDD_E_UNSUPPORTED;
     if (fast) {
-        rc = launch_ctc_fast(p, ws + w.off_fast, st);           // flags[b] != 0 -> utterance needs the log-space path
+        // flags[b] != 0 on return -> utterance needs the log-space path
+        rc = algo == 3 ? launch_ctc_fast(p, ws + w.off_fast, st) : launch_ctc_pair(p, ws + w.off_fast, st);
         if (rc) return rc;
-        if (algo == 0) {
+        if (algo == 0 || algo == 3) {
             p.only_flagged = 1;
             rc = launch_ctc_log(p, st);
             if (rc) return rc;

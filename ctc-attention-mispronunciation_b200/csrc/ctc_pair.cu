@@ -1,0 +1,745 @@
+// ctc_pair.cu -- CTC loss + gradient, default fast path of mdd_ctc_loss: two utterances per warp, packed FP32.
+//
+// Semantics: torch aten ctc_loss / _ctc_loss_backward as reached from nn.CTCLoss at
+// egs/attention_aug/steps/train_ctc.py:186,72,96 and egs/cnn-rnn-ctc/steps/train_ctc.py:148,51,67.
+//
+// The lattice recursion is bound by instruction issue and by shared-memory wavefronts, not by HBM, so
+// this kernel is organised around issuing as few instructions per lattice state as possible:
+//
+//  * One warp owns a PAIR of utterances.  Lane l holds NSL consecutive extended-label states of both utterances as
+//    float2 registers (.x = first utterance, .y = second); every lattice update is a packed sm_100 instruction
+//    (FADD2 / FFMA2 / FMUL2), i.e. half the FP32 issue slots of a scalar kernel.  Neighbour states across lanes come
+//    from warp shuffles; there is no block barrier anywhere.
+//  * Linear domain with block floating point (as ctc_fast.cu): emissions are exponentiated once per (t,c); alpha is
+//    renormalised once per chunk of KF = 8 frames from each lane's own maximum, a max-scan keeps a lane within 2^GAP
+//    of the lane it receives from.  The checkpoint of a chunk is taken AFTER its renormalisation, so the recomputation
+//    in the backward sweep needs no renormalisation at all and is bitwise the forward's.
+//  * beta has no normalisation of its own: its per-lane exponent is DEFINED as  e_beta = e_P + OFF - e_alpha  (e_P the
+//    exponent of the total likelihood P).  Because alpha_t(s) * u_t(s) <= P for every state (u = beta without the
+//    emission at t), the beta mantissas are bounded by 2^-OFF / (alpha mantissa), and whatever underflows belongs to
+//    paths of relative mass < 2^-75.  The products alpha * u of all lanes are then on ONE common scale, sum_s = P, so
+//    neither a per-frame normaliser nor the blank states' products are needed:
+//        occupancy_c / Z = (sum_{s: l'_s = c} alpha u) * (2^OFF / mantissa(P)),  occupancy_blank = Z - sum of labels.
+//  * Ragged pairs: frames [0, min(T0,T1)) are processed jointly, then the longer utterance alone (the other half runs
+//    on zero emissions, stays finite, and its gradient rows are written as zeros).  Chunks never straddle the boundary.
+//  * Class reduction: label products are scattered into a class-sorted row, prefix-summed in place with 128-bit
+//    accesses (lane = frame x utterance x half of the list), class occupancy = P[last] - P[first-1].  No atomics:
+//    results are bitwise reproducible.
+//  * Anything unusual (infeasible, empty, malformed, over/underflow) sets flags[b]; ctc_log.cu redoes exactly those
+//    utterances in the same stream with torch's inf / NaN / zero_infinity semantics.
+#include <cstdlib>
+
+#include "common.cuh"
+#include "ctc_params.cuh"
+
+namespace mdd {
+namespace {
+
+constexpr int KF = 8;                    // frames per chunk = renormalisation period = checkpoint period
+constexpr int E_EMPTY = -(1 << 20);      // exponent of a lane whose states are all zero
+constexpr int OFF = 50;                  // beta mantissas are kept 2^-OFF below 1 / (alpha mantissa)
+constexpr int CPMAX = 68;                // staged emission row: utterance h at [h*CPMAX, h*CPMAX + C], C <= 64
+constexpr int RW = 2 * CPMAX;
+constexpr unsigned FULL = 0xffffffffu;
+
+template <int NSL>
+struct PGeo {
+    static constexpr int NL = NSL / 2;                     // label states per lane
+    static constexpr int LCAP = 16 * NSL - 1;              // S = 2L+1 <= 32*NSL - 1
+    static constexpr int U1OFF = ((LCAP + 3 + 3) & ~3) + 4;    // second utterance's sorted list inside a product row
+    static constexpr int ZERO = U1OFF - 1;                 // always 0
+    static constexpr int DUMP = U1OFF - 2;                 // swallows products of unused label slots
+    static constexpr int RS = ((U1OFF + LCAP + 3 - 4 + 31) / 32) * 32 + 4;   // product row stride, == 4 (mod 32)
+    // mass can cross ceil(2*KF/NSL)+1 lane boundaries between two renormalisations, each multiplying the mantissa by
+    // up to 2^GAP, plus 3^KF of growth: GAP * crossings + 14 < 126
+    static constexpr int GAP = NSL == 2 ? 12 : NSL == 4 ? 22 : NSL == 8 ? 36 : 56;
+    static constexpr int CKW = 32 * (2 * NSL + 2);         // checkpoint words per pair and chunk
+};
+
+__device__ __forceinline__ float pow2i(int x) {            // 2^x, 0 below the normal range, clamped at 2^127
+    return x < -126 ? 0.f : __int_as_float((127 + min(x, 127)) << 23);
+}
+__device__ __forceinline__ float fast_exp(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+    return y;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float m;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(m) : "f"(a), "f"(b), "f"(c));
+    return m;
+}
+__device__ __forceinline__ float compc(const float2& v, int h) { return h ? v.y : v.x; }
+
+// Two floats per lane per utterance row.  VEC: columns (2*lane, 2*lane+1) as one 8-byte access, else (lane, lane+32).
+struct Cols {
+    int c0, c1;
+    bool v0, v1;
+    int l0, l1;
+};
+template <bool VEC>
+__device__ __forceinline__ Cols make_cols(int lane, int C) {
+    Cols k;
+    if constexpr (VEC) { k.c0 = 2 * lane; k.c1 = 2 * lane + 1; k.v0 = k.v1 = (2 * lane < C); }
+    else { k.c0 = lane; k.c1 = lane + 32; k.v0 = lane < C; k.v1 = lane + 32 < C; }
+    k.l0 = k.v0 ? k.c0 : 0;
+    k.l1 = k.v1 ? k.c1 : 0;
+    return k;
+}
+template <bool VEC>
+__device__ __forceinline__ float2 ld_row2(const float* __restrict__ src, const Cols& k) {
+    if constexpr (VEC) return __ldcs(reinterpret_cast<const float2*>(src + k.l0));
+    else return make_float2(__ldcs(src + k.l0), __ldcs(src + k.l1));
+}
+template <bool VEC>
+__device__ __forceinline__ void st_row2_smem(float* __restrict__ dst, const Cols& k, float2 v) {
+    if constexpr (VEC) { if (k.v0) *reinterpret_cast<float2*>(dst + k.c0) = v; }
+    else { if (k.v0) dst[k.c0] = v.x; if (k.v1) dst[k.c1] = v.y; }
+}
+template <bool VEC>
+__device__ __forceinline__ float2 ld_row2_smem(const float* __restrict__ src, const Cols& k) {
+    if constexpr (VEC) return *reinterpret_cast<const float2*>(src + k.l0);
+    else return make_float2(src[k.l0], src[k.l1]);
+}
+template <bool VEC>
+__device__ __forceinline__ void st_row2_gmem(float* __restrict__ dst, const Cols& k, float2 v) {
+    if constexpr (VEC) { if (k.v0) __stcs(reinterpret_cast<float2*>(dst + k.c0), v); }
+    else { if (k.v0) __stcs(dst + k.c0, v.x); if (k.v1) __stcs(dst + k.c1, v.y); }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// One lattice step for both utterances.  Lane l owns states s = NSL*l + j; even j = blank, odd j = label (j-1)/2.
+//   alpha: new[s] = (a[s] + a[s-1] + ma * a[s-2]) * e[s]
+//   beta : u[s]   =  b[s] + b[s+1] + mb * b[s+2];  new b[s] = u[s] * e[s]
+// ep0/ep1 point at the emission of my label states inside the staged row of frame 0 (unused slots read a zero).
+// ---------------------------------------------------------------------------------------------------------------
+template <int NSL>
+__device__ __forceinline__ void alpha_step(float2 (&a)[NSL], float2 sc, int roff, const float* __restrict__ bl0,
+                                           const float* __restrict__ bl1, const float* const (&ep0)[NSL / 2],
+                                           const float* const (&ep1)[NSL / 2], const float2 (&ma)[NSL / 2]) {
+    float2 p = make_float2(__shfl_up_sync(FULL, a[NSL - 1].x, 1), __shfl_up_sync(FULL, a[NSL - 1].y, 1));
+    p = __fmul2_rn(p, sc);                                       // sc == 0 on lane 0
+    const float2 eb = make_float2(bl0[roff], bl1[roff]);
+    float2 e[NSL / 2];
+#pragma unroll
+    for (int q = 0; q < NSL / 2; ++q) e[q] = make_float2(ep0[q][roff], ep1[q][roff]);
+    float2 n[NSL];
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) {
+        const float2 m1 = j ? a[j - 1] : p;
+        if (j & 1) {
+            const float2 m2 = j >= 2 ? a[j - 2] : p;
+            n[j] = __fmul2_rn(__ffma2_rn(ma[j >> 1], m2, __fadd2_rn(a[j], m1)), e[j >> 1]);
+        } else {
+            n[j] = __fmul2_rn(__fadd2_rn(a[j], m1), eb);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) a[j] = n[j];
+}
+
+template <int NSL>
+__device__ __forceinline__ void beta_step(float2 (&b)[NSL], float2 (&ul)[NSL / 2], float2 sc, int roff,
+                                          const float* __restrict__ bl0, const float* __restrict__ bl1,
+                                          const float* const (&ep0)[NSL / 2], const float* const (&ep1)[NSL / 2],
+                                          const float2 (&mb)[NSL / 2]) {
+    float2 n0 = make_float2(__shfl_down_sync(FULL, b[0].x, 1), __shfl_down_sync(FULL, b[0].y, 1));
+    float2 n1 = make_float2(__shfl_down_sync(FULL, b[1].x, 1), __shfl_down_sync(FULL, b[1].y, 1));
+    n0 = __fmul2_rn(n0, sc);                                     // sc == 0 on lane 31
+    n1 = __fmul2_rn(n1, sc);
+    const float2 eb = make_float2(bl0[roff], bl1[roff]);
+    float2 e[NSL / 2];
+#pragma unroll
+    for (int q = 0; q < NSL / 2; ++q) e[q] = make_float2(ep0[q][roff], ep1[q][roff]);
+    float2 n[NSL];
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) {
+        const float2 p1 = (j + 1 < NSL) ? b[j + 1] : n0;
+        if (j & 1) {
+            const float2 p2 = (j + 2 < NSL) ? b[j + 2] : n1;
+            const float2 u = __ffma2_rn(mb[j >> 1], p2, __fadd2_rn(b[j], p1));
+            ul[j >> 1] = u;
+            n[j] = __fmul2_rn(u, e[j >> 1]);
+        } else {
+            n[j] = __fmul2_rn(__fadd2_rn(b[j], p1), eb);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) b[j] = n[j];
+}
+
+// Per-lane renormalisation of alpha for both utterances (see the header).  ok[h] = false if utterance h has no
+// alignment mass left or real content had to be squashed by more than 2^100.
+template <int NSL>
+__device__ __forceinline__ void renorm_alpha(float2 (&a)[NSL], int (&ea)[2], float2& sca, int lane, bool (&ok)[2]) {
+    constexpr int GAP = PGeo<NSL>::GAP;
+    float f[2], sc[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        float m = compc(a[0], h);
+#pragma unroll
+        for (int j = 1; j + 1 < NSL; j += 2) m = fmax3(m, compc(a[j], h), compc(a[j + 1], h));
+        m = fmaxf(m, compc(a[NSL - 1], h));
+        const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;
+        const bool some = m >= 1.17549435e-38f && m < 3.0e38f;       // normal, finite (NaN fails both)
+        const int e_own = some ? ea[h] + k : E_EMPTY;
+        int t = e_own + GAP * lane;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) t = max(t, __shfl_up_sync(FULL, t, d));   // lanes < d get their own value back
+        const int e_new = t - GAP * lane;
+        f[h] = pow2i(ea[h] - e_new);
+        ea[h] = e_new;
+        const int e_nb = __shfl_up_sync(FULL, e_new, 1);
+        sc[h] = lane == 0 ? 0.f : pow2i(e_nb - e_new);
+        const bool bad = (m != m) || m >= 3.0e38f || (some && e_new - e_own > 100);
+        ok[h] = __any_sync(FULL, some) && !__any_sync(FULL, bad);
+    }
+    const float2 f2 = make_float2(f[0], f[1]);
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) a[j] = __fmul2_rn(a[j], f2);
+    sca = make_float2(sc[0], sc[1]);
+}
+
+struct PairSmem {
+    int prod_off, rows_off, abuf_off, total_floats;
+};
+__host__ __device__ inline PairSmem pair_smem_layout(int NSL, int RS, bool regbuf) {
+    PairSmem s;
+    int o = 0;
+    s.prod_off = o; o += KF * RS;                 // class-sorted label products -> prefix sums (setup scratch too)
+    s.rows_off = o; o += KF * RW;                 // exp(lp) rows of the current chunk, both utterances
+    s.abuf_off = o; if (!regbuf) o += KF * (NSL / 2) * 64;    // alpha label states of the chunk (float2 per lane)
+    s.total_floats = (o + 3) & ~3;
+    return s;
+}
+
+template <int NSL, bool VEC, bool REGBUF>
+__global__ void __launch_bounds__(128)
+ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
+    using G = PGeo<NSL>;
+    constexpr int NL = G::NL, RS = G::RS, U1OFF = G::U1OFF, ZERO = G::ZERO, DUMP = G::DUMP, CKW = G::CKW;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int pair = blockIdx.x * (blockDim.x >> 5) + warp;
+    const int npairs = (p.B + 1) >> 1;
+    if (pair >= npairs) return;
+
+    extern __shared__ __align__(16) float smem_f[];
+    const PairSmem lay = pair_smem_layout(NSL, RS, REGBUF);
+    float* base = smem_f + (size_t)warp * lay.total_floats;
+    float* prod = base + lay.prod_off;                           // [KF][RS]
+    float* rows = base + lay.rows_off;                           // [KF][RW]
+    float2* abuf = reinterpret_cast<float2*>(base + lay.abuf_off);   // [KF][NL][32]
+
+    const int C = p.C, blank = p.blank, T = p.T;
+    const bool want_grad = p.grad != nullptr;
+
+    // ------------------------------------------------------------------------------------------ per-utterance setup
+    int bidx[2], Tb[2], L[2], S[2];
+    bool act[2];
+    int* scratch = reinterpret_cast<int*>(prod);                 // lab[2][256] | slot[2][256] | ctab[2][128]
+    int* lab = scratch;
+    int* slot = scratch + 512;
+    int* ctab = scratch + 1024;
+    static_assert(KF * (G::RS + RW) >= 1280, "setup scratch must fit in the product + emission rows");
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int b = 2 * pair + h;
+        bidx[h] = b;
+        act[h] = b < p.B;
+        Tb[h] = 0; L[h] = 0;
+        if (act[h]) {
+            const long long Tb64 = p.in_len[b], L64 = p.tgt_len[b];
+            bool bad = Tb64 <= 0 || Tb64 > T || L64 < 0 || L64 > p.Lmax || L64 > G::LCAP;
+            if (!bad) {
+                const int64_t* tg = p.tgt_stride ? p.targets + (int64_t)b * p.tgt_stride : p.targets + p.tgt_offsets[b];
+                int fl = 0;
+                for (int i = lane; i < (int)L64; i += 32) {
+                    const long long v = tg[i];
+                    if (v < 0 || v >= C || v == blank) fl = 1;
+                    lab[h * 256 + i] = (int)v;
+                }
+                bad = __any_sync(FULL, fl);
+            }
+            if (bad) {
+                if (lane == 0) p.flags[b] = 1;                   // the log-space kernel owns the error reporting
+                act[h] = false;
+            } else {
+                Tb[h] = (int)Tb64;
+                L[h] = (int)L64;
+            }
+        }
+        S[h] = 2 * L[h] + 1;
+    }
+    if (!act[0] && !act[1]) return;
+    __syncwarp();
+
+    const Cols cols = make_cols<VEC>(lane, C);
+
+    // per-lane constants: emission pointers and skip masks of my label states
+    const float* ep0[NL];
+    const float* ep1[NL];
+    float2 ma[NL], mb[NL];
+#pragma unroll
+    for (int q = 0; q < NL; ++q) {
+        const int i = lane * NL + q;
+        int eo[2];
+        float am[2], bm[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const bool in = i < L[h];
+            const int c = in ? lab[h * 256 + i] : -1;
+            eo[h] = in ? h * CPMAX + c : C;                      // rows[r][C] == 0
+            am[h] = (in && i > 0 && lab[h * 256 + i - 1] != c) ? 1.f : 0.f;
+            bm[h] = (in && i + 1 < L[h] && lab[h * 256 + i + 1] != c) ? 1.f : 0.f;
+        }
+        ep0[q] = rows + eo[0];
+        ep1[q] = rows + eo[1];
+        ma[q] = make_float2(am[0], am[1]);
+        mb[q] = make_float2(bm[0], bm[1]);
+    }
+    const float* bl0 = rows + blank;
+    const float* bl1 = rows + CPMAX + blank;
+
+    // class-sorted slots.  Label i of utterance h gets slot perm(i) of a list sorted by class (positions ascending
+    // inside a class), cut at the class boundary nearest L/2 into two stretches; the second starts 16-byte aligned.
+    float* pp0[NL];                                              // product slot of my label states (frame 0)
+    float* pp1[NL];
+    const float* pli[4];                                         // occupancy = sg * P[li] + cst - P[lj]
+    const float* plj[4];
+    float sg[4];
+    bool isblank[4];
+    int st_split[2], st_pad[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int Lh = L[h];
+        int cnt[2] = {0, 0};
+        for (int i = 0; i < Lh; ++i) {
+            const int v = lab[h * 256 + i];
+            cnt[0] += (v == lane);
+            cnt[1] += (v == lane + 32);
+        }
+        int start[2], basek = 0;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            int inc = cnt[k];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(FULL, inc, d);
+                if (lane >= d) inc += o;
+            }
+            start[k] = basek + inc - cnt[k];
+            basek += __shfl_sync(FULL, inc, 31);
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int c = lane + 32 * k;
+            ctab[h * 128 + c] = start[k];
+            ctab[h * 128 + 64 + c] = cnt[k];
+            if (cnt[k] > 0) {
+                int w = start[k];
+                for (int i = 0; i < Lh; ++i)
+                    if (lab[h * 256 + i] == c) slot[h * 256 + i] = w++;
+            }
+        }
+        int best = 0x7fffffff;
+        const int want = Lh >> 1;
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+            if (cnt[k] > 0) best = min(best, abs(start[k] - want) * 1024 + start[k]);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(FULL, best, d));
+        const int split = (best == 0x7fffffff) ? 0 : (best & 1023);
+        const int pad = ((split + 3) & ~3) - split;
+        st_split[h] = split;
+        st_pad[h] = pad;
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < NL; ++q) {
+            const int i = lane * NL + q;
+            int s = DUMP;
+            if (i < Lh) {
+                const int sp = slot[h * 256 + i];
+                s = h * U1OFF + sp + (sp >= split ? pad : 0);
+            }
+            if (h == 0) pp0[q] = prod + s; else pp1[q] = prod + s;
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int c = k ? cols.c1 : cols.c0;
+            const bool valid = k ? cols.v1 : cols.v0;
+            int oi = ZERO, oj = ZERO;
+            float sgn = 1.f;
+            bool isb = false;
+            if (valid && c == blank) {                            // Z - (total of stretch 0) - (total of stretch 1)
+                isb = true;
+                sgn = -1.f;
+                if (split > 0) oi = h * U1OFF + split - 1;
+                if (Lh > split) oj = h * U1OFF + Lh + pad - 1;
+            } else if (valid) {
+                const int st = ctab[h * 128 + c], n = ctab[h * 128 + 64 + c];
+                if (n > 0) {
+                    const int stp = st + (st >= split ? pad : 0);
+                    oi = h * U1OFF + stp + n - 1;
+                    if (!(st == 0 || st == split)) oj = h * U1OFF + stp - 1;
+                }
+            }
+            pli[2 * h + k] = prod + oi;
+            plj[2 * h + k] = prod + oj;
+            sg[2 * h + k] = sgn;
+            isblank[2 * h + k] = isb;
+        }
+    }
+    __syncwarp();
+    // zero pads of the staged rows (emission of unused label slots) and the ZERO slot of the product rows
+    if (lane < KF) {
+        for (int c = C; c < CPMAX; ++c) rows[lane * RW + c] = 0.f;
+        for (int c = C; c < CPMAX; ++c) rows[lane * RW + CPMAX + c] = 0.f;
+        prod[lane * RS + ZERO] = 0.f;
+    }
+    __syncwarp();
+
+    // ------------------------------------------------------------------------------------------ geometry
+    const int Tmin = min(Tb[0], Tb[1]), Tmax = max(Tb[0], Tb[1]);
+    const int nJ = (Tmin + KF - 1) / KF, nch = nJ + (Tmax - Tmin + KF - 1) / KF;
+    auto chunk_geom = [&](int j, int& t0, int& n) {
+        if (j < nJ) { t0 = j * KF; n = min(KF, Tmin - t0); }
+        else { t0 = Tmin + (j - nJ) * KF; n = min(KF, Tmax - t0); }
+    };
+    // rows are always read from a live utterance's memory; an idle half re-reads its partner's rows
+    const int bsrc0 = act[0] ? bidx[0] : bidx[1], bsrc1 = act[1] ? bidx[1] : bidx[0];
+    const float* lp0 = p.lp + (size_t)bsrc0 * p.stride_b;
+    const float* lp1 = p.lp + (size_t)bsrc1 * p.stride_b;
+    const size_t gstride = (size_t)p.B * C;
+    float* gr0 = want_grad ? p.grad + (size_t)bidx[0] * C : nullptr;
+    float* gr1 = want_grad ? p.grad + (size_t)bidx[1] * C : nullptr;
+    float g[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) g[h] = act[h] ? (p.grad_out ? p.grad_out[bidx[h]] : 1.f) * p.gscalar : 0.f;
+
+    float2 pre0[KF], pre1[KF];                          // the next chunk's rows, in flight
+    auto load_rows = [&](int j) {                       // rows past the end of a partial chunk re-read its last row
+        int t0, n;
+        chunk_geom(j, t0, n);
+        const float* s0 = lp0 + (size_t)t0 * p.stride_t;
+        const float* s1 = lp1 + (size_t)t0 * p.stride_t;
+#pragma unroll
+        for (int r = 0; r < KF; ++r) {
+            const size_t o = (size_t)min(r, n - 1) * p.stride_t;
+            pre0[r] = ld_row2<VEC>(s0 + o, cols);
+            pre1[r] = ld_row2<VEC>(s1 + o, cols);
+        }
+    };
+    auto commit_rows = [&](bool kill0, bool kill1) {    // p = exp(lp) into shared memory; an idle half emits zeros
+#pragma unroll
+        for (int r = 0; r < KF; ++r) {
+            float2 v0 = make_float2(fast_exp(pre0[r].x), fast_exp(pre0[r].y));
+            float2 v1 = make_float2(fast_exp(pre1[r].x), fast_exp(pre1[r].y));
+            if (kill0) v0 = make_float2(0.f, 0.f);
+            if (kill1) v1 = make_float2(0.f, 0.f);
+            st_row2_smem<VEC>(rows + r * RW, cols, v0);
+            st_row2_smem<VEC>(rows + r * RW + CPMAX, cols, v1);
+        }
+    };
+
+    // ------------------------------------------------------------------------------------------ forward sweep
+    float2 a[NSL];
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) a[j] = make_float2(0.f, 0.f);
+    if (lane == 0) a[0] = make_float2(act[0] ? 1.f : 0.f, act[1] ? 1.f : 0.f);   // virtual alpha_{-1}
+    int ea[2] = {0, 0};
+    float2 sca = make_float2(0.f, 0.f);
+    int flag[2] = {0, 0};
+    float zi[2] = {0.f, 0.f}, zc[2] = {0.f, 0.f};
+    int koff[2] = {0, 0};
+    float* ck = ckpt_ws + (size_t)pair * n_ckpt * CKW;
+
+    load_rows(0);
+    if (want_grad) {                                    // rows t >= T_max of the gradient are zero (torch semantics)
+        for (int t = Tmax; t < T; ++t) {
+            if (act[0]) st_row2_gmem<VEC>(gr0 + (size_t)t * gstride, cols, make_float2(0.f, 0.f));
+            if (act[1]) st_row2_gmem<VEC>(gr1 + (size_t)t * gstride, cols, make_float2(0.f, 0.f));
+        }
+    }
+
+    for (int j = 0; j < nch; ++j) {
+        int t0, n;
+        chunk_geom(j, t0, n);
+        const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
+        __syncwarp();
+        commit_rows(kill0, kill1);
+        __syncwarp();
+        if (j + 1 < nch) load_rows(j + 1);
+        {
+            bool ok[2];
+            renorm_alpha<NSL>(a, ea, sca, lane, ok);
+            if (!ok[0] && !kill0 && !flag[0]) flag[0] = 2 | (t0 << 8);
+            if (!ok[1] && !kill1 && !flag[1]) flag[1] = 2 | (t0 << 8);
+        }
+        if (want_grad) {                                // alpha entering chunk j, after its renormalisation
+            float* c = ck + (size_t)j * CKW;
+#pragma unroll
+            for (int q = 0; q < NSL / 2; ++q)
+                reinterpret_cast<float4*>(c)[q * 32 + lane] = make_float4(a[2 * q].x, a[2 * q].y, a[2 * q + 1].x, a[2 * q + 1].y);
+            reinterpret_cast<int2*>(c + 64 * NSL)[lane] = make_int2(ea[0], ea[1]);
+        }
+#pragma unroll
+        for (int r = 0; r < KF; ++r)
+            if (r < n) alpha_step<NSL>(a, sca, r * RW, bl0, bl1, ep0, ep1, ma);
+        const int tend = t0 + n;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (act[h] && tend == Tb[h]) {
+                // P = alpha_{T-1}(S-1) + alpha_{T-1}(S-2), possibly in two lanes with different exponents
+                float v = 0.f;
+#pragma unroll
+                for (int jj = 0; jj < NSL; ++jj) {
+                    const int s = lane * NSL + jj;
+                    if (s == S[h] - 1 || s == S[h] - 2) v += compc(a[jj], h);
+                }
+                int em = (v > 0.f) ? ea[h] : E_EMPTY;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) em = max(em, __shfl_xor_sync(FULL, em, d));
+                v = warp_sum(v * pow2i(ea[h] - em));
+                if ((em == E_EMPTY || !(v > 1e-30f) || v > 1e37f) && !flag[h]) flag[h] = 3;
+                if (!flag[h]) {
+                    if (lane == 0) {
+                        p.nll[bidx[h]] = (float)(-((double)logf(v) + (double)em * 0.69314718055994530942));
+                        if (p.status) p.status[bidx[h]] = MDD_ST_OK;
+                    }
+                    zc[h] = v * pow2i(-OFF);
+                    zi[h] = pow2i(OFF) / v;
+                    koff[h] = em + OFF;
+                }
+            }
+        }
+    }
+    if (!want_grad || ((flag[0] || !act[0]) && (flag[1] || !act[1]))) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (act[h] && lane == 0) p.flags[bidx[h]] = flag[h];
+        return;
+    }
+
+    // ------------------------------------------------------------------------------------------ backward sweep
+    float2 bt[NSL];
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) bt[j] = make_float2(0.f, 0.f);
+    int eb[2] = {0, 0};
+    float cst[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) cst[k] = isblank[k] ? zc[k >> 1] : 0.f;
+    // scan role of this lane: frame f, utterance sh, stretch part
+    const int sf = lane & (KF - 1), sh = (lane >> 3) & 1, spart = lane >> 4;
+    const int s_split = sh ? st_split[1] : st_split[0], s_pad = sh ? st_pad[1] : st_pad[0], s_L = sh ? L[1] : L[0];
+    const int kb = sh * U1OFF + (spart ? s_split + s_pad : 0);
+    const int ke = sh * U1OFF + (spart ? s_L + s_pad : s_split);
+    int bad_occ = 0;
+
+    if (nch >= 2) load_rows(nch - 2);
+    for (int j = nch - 1; j >= 0; --j) {
+        int t0, n;
+        chunk_geom(j, t0, n);
+        const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
+        if (j < nch - 1) {                              // the last chunk is still staged (and exponentiated)
+            __syncwarp();
+            commit_rows(kill0, kill1);
+            __syncwarp();
+            if (j > 0) load_rows(j - 1);
+        }
+        // alpha entering the chunk (post-renormalisation) and the exponents that go with it
+        {
+            const float* c = ck + (size_t)j * CKW;
+#pragma unroll
+            for (int q = 0; q < NSL / 2; ++q) {
+                const float4 v = reinterpret_cast<const float4*>(c)[q * 32 + lane];
+                a[2 * q] = make_float2(v.x, v.y);
+                a[2 * q + 1] = make_float2(v.z, v.w);
+            }
+            const int2 e2 = reinterpret_cast<const int2*>(c + 64 * NSL)[lane];
+            ea[0] = e2.x; ea[1] = e2.y;
+        }
+        float2 scb;
+        {
+            float fb[2], sa[2], sb[2], ini[2];
+            const int tend = t0 + n;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int el = __shfl_up_sync(FULL, ea[h], 1), er = __shfl_down_sync(FULL, ea[h], 1);
+                sa[h] = lane == 0 ? 0.f : pow2i(el - ea[h]);
+                sb[h] = lane == 31 ? 0.f : pow2i(ea[h] - er);            // 2^(e_beta[l+1] - e_beta[l])
+                const int ebn = koff[h] - ea[h];
+                const bool starts = act[h] && tend == Tb[h];             // beta_T enters here
+                fb[h] = starts ? 0.f : pow2i(eb[h] - ebn);
+                ini[h] = starts ? pow2i(-ebn) : 0.f;
+                // beta_T = 1 must be representable in the lane that owns state S-1
+                const bool owner = (S[h] - 1) / NSL == lane;
+                if (__any_sync(FULL, starts && owner && (ebn > 120 || ebn < -120)) && !flag[h]) flag[h] = 6;
+                eb[h] = ebn;
+            }
+            sca = make_float2(sa[0], sa[1]);
+            scb = make_float2(sb[0], sb[1]);
+            const float2 f2 = make_float2(fb[0], fb[1]);
+#pragma unroll
+            for (int jj = 0; jj < NSL; ++jj) {
+                bt[jj] = __fmul2_rn(bt[jj], f2);
+                const int s = lane * NSL + jj;
+                if (s == S[0] - 1) bt[jj].x += ini[0];
+                if (s == S[1] - 1) bt[jj].y += ini[1];
+            }
+        }
+        // recompute alpha over the chunk, keeping the label states
+        float2 A[REGBUF ? KF : 1][NL];
+#pragma unroll
+        for (int r = 0; r < KF; ++r) {
+            if (r < n) {
+                alpha_step<NSL>(a, sca, r * RW, bl0, bl1, ep0, ep1, ma);
+#pragma unroll
+                for (int q = 0; q < NL; ++q) {
+                    if constexpr (REGBUF) A[r][q] = a[2 * q + 1];
+                    else abuf[(r * NL + q) * 32 + lane] = a[2 * q + 1];
+                }
+            }
+        }
+        __syncwarp();                                   // the previous chunk's gradient rows have been read
+        // beta over the chunk; label products alpha_t(s) * u_t(s) into their class-sorted slots
+#pragma unroll
+        for (int r = KF - 1; r >= 0; --r) {
+            if (r < n) {
+                float2 ul[NL];
+                beta_step<NSL>(bt, ul, scb, r * RW, bl0, bl1, ep0, ep1, mb);
+#pragma unroll
+                for (int q = 0; q < NL; ++q) {
+                    float2 al;
+                    if constexpr (REGBUF) al = A[r][q];
+                    else al = abuf[(r * NL + q) * 32 + lane];
+                    const float2 pl = __fmul2_rn(al, ul[q]);
+                    pp0[q][r * RS] = pl.x;
+                    pp1[q][r * RS] = pl.y;
+                }
+            }
+        }
+        __syncwarp();
+        // in-place prefix sums of the sorted products: lane = (frame, utterance, stretch)
+        if (sf < n) {
+            float* pr = prod + sf * RS;
+            float acc = 0.f;
+            for (int k = kb; k < ke; k += 4) {
+                float4 v = *reinterpret_cast<float4*>(pr + k);
+                acc += v.x; v.x = acc;
+                acc += v.y; v.y = acc;
+                acc += v.z; v.z = acc;
+                acc += v.w; v.w = acc;
+                *reinterpret_cast<float4*>(pr + k) = v;
+            }
+        }
+        __syncwarp();
+        // gradient rows of the chunk: (softmax prob - occupancy / Z) * g
+        {
+            const float g0 = kill0 ? 0.f : g[0], g1 = kill1 ? 0.f : g[1];
+            const float zg0 = zi[0] * g0, zg1 = zi[1] * g1;
+#pragma unroll
+            for (int r = 0; r < KF; ++r) {
+                if (r < n) {
+                    const float2 pv0 = ld_row2_smem<VEC>(rows + r * RW, cols);
+                    const float2 pv1 = ld_row2_smem<VEC>(rows + r * RW + CPMAX, cols);
+                    float o[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) o[k] = fmaf(sg[k], pli[k][r * RS], cst[k]) - plj[k][r * RS];
+                    // every occupancy must be a number >= 0 up to rounding: catches overflow / NaN anywhere upstream
+                    if (!(o[0] >= -1e-3f * zc[0]) || !(o[1] >= -1e-3f * zc[0])) bad_occ |= kill0 ? 0 : 1;
+                    if (!(o[2] >= -1e-3f * zc[1]) || !(o[3] >= -1e-3f * zc[1])) bad_occ |= kill1 ? 0 : 2;
+                    const size_t go = (size_t)(t0 + r) * gstride;
+                    if (act[0])
+                        st_row2_gmem<VEC>(gr0 + go, cols, make_float2(fmaf(-o[0], zg0, pv0.x * g0), fmaf(-o[1], zg0, pv0.y * g0)));
+                    if (act[1])
+                        st_row2_gmem<VEC>(gr1 + go, cols, make_float2(fmaf(-o[2], zg1, pv1.x * g1), fmaf(-o[3], zg1, pv1.y * g1)));
+                }
+            }
+        }
+    }
+    {   // beta must have stayed finite to the very first frame (a blank state's overflow shows nowhere else)
+#pragma unroll
+        for (int jj = 0; jj < NSL; ++jj) {
+            if (!(bt[jj].x < 3.0e38f)) bad_occ |= 1;
+            if (!(bt[jj].y < 3.0e38f)) bad_occ |= 2;
+        }
+        bad_occ = __reduce_or_sync(FULL, bad_occ);
+        if ((bad_occ & 1) && !flag[0]) flag[0] = 5;
+        if ((bad_occ & 2) && !flag[1]) flag[1] = 5;
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (act[h] && lane == 0) p.flags[bidx[h]] = flag[h];   // 0 = done here; else redone in log space
+    }
+}
+
+int pick_nsl(int Lmax) {
+    if (Lmax <= PGeo<2>::LCAP) return 2;
+    if (Lmax <= PGeo<4>::LCAP) return 4;
+    if (Lmax <= PGeo<8>::LCAP) return 8;
+    if (Lmax <= PGeo<16>::LCAP) return 16;
+    return 0;
+}
+
+int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+template <int NSL, bool VEC, bool REGBUF>
+int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
+    const PairSmem lay = pair_smem_layout(NSL, PGeo<NSL>::RS, REGBUF);
+    const size_t per_warp = (size_t)lay.total_floats * 4;
+    const int npairs = (p.B + 1) / 2;
+    static int wpc_env = env_int("MDD_CTC_PAIR_WPC", 2);
+    int warps = wpc_env < 1 ? 1 : wpc_env > 4 ? 4 : wpc_env;
+    const int spread = (npairs + kNumSM - 1) / kNumSM;           // small batches: one warp per SM first
+    if (warps > spread) warps = spread > 0 ? spread : 1;
+    const size_t smem = per_warp * warps;
+    static bool configured = false;
+    if (!configured) {
+        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, VEC, REGBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)(per_warp * 4)) != cudaSuccess) {
+            cudaGetLastError();
+            return MDD_E_CUDA;
+        }
+        configured = true;
+    }
+    const int n_ckpt = (p.T + KF - 1) / KF + 2;
+    const int grid = (npairs + warps - 1) / warps;
+    ctc_pair_kernel<NSL, VEC, REGBUF><<<grid, warps * 32, smem, st>>>(p, ws, n_ckpt);
+    MDD_CHECK_LAUNCH();
+    return MDD_OK;
+}
+
+template <int NSL>
+int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
+    const bool vec = (p.C % 2 == 0) && (p.stride_t % 2 == 0) && (p.stride_b % 2 == 0) && ((uintptr_t)p.lp % 8 == 0) &&
+                     (!p.grad || (uintptr_t)p.grad % 8 == 0);
+    static int regbuf = env_int("MDD_CTC_PAIR_REGBUF", 1);
+    if (regbuf) return vec ? launch_cfg<NSL, true, true>(p, ws, st) : launch_cfg<NSL, false, true>(p, ws, st);
+    return vec ? launch_cfg<NSL, true, false>(p, ws, st) : launch_cfg<NSL, false, false>(p, ws, st);
+}
+
+}  // namespace
+
+bool ctc_pair_supported(int C, int Lmax) { return C <= 64 && pick_nsl(Lmax) != 0; }
+
+size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
+    const int nsl = pick_nsl(Lmax);
+    if (!nsl) return 0;
+    const size_t n_ckpt = (size_t)(T + KF - 1) / KF + 2;
+    return (size_t)((B + 1) / 2) * n_ckpt * 32 * (2 * nsl + 2) * 4;
+}
+
+int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st) {
+    float* w = reinterpret_cast<float*>(ws);
+    switch (pick_nsl(p.Lmax)) {
+        case 2: return launch_nsl<2>(p, w, st);
+        case 4: return launch_nsl<4>(p, w, st);
+        case 8: return launch_nsl<8>(p, w, st);
+        case 16: return launch_nsl<16>(p, w, st);
+        default: return MDD_E_UNSUPPORTED;
+    }
+}
+
+}  // namespace mdd

@@ -39,6 +39,11 @@ bool ctc_fast_supported(int C, int Lmax);
 size_t ctc_fast_ws_bytes(int T, int B, int Lmax);
 int launch_ctc_fast(CtcParams p, void* ws, cudaStream_t st);
 
+// two utterances per warp, packed FP32 (ctc_pair.cu): the default fast path
+bool ctc_pair_supported(int C, int Lmax);
+size_t ctc_pair_ws_bytes(int T, int B, int Lmax);
+int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st);
+
 // deterministic sum of nll[B] -> loss_sum (reduce.cu)
 int launch_sum_nll(const float* nll, int B, float* out, cudaStream_t st);
 int launch_scale_grad(float* grad, int T, int B, int C, const float* scale, float scalar, cudaStream_t st);
