@@ -28,6 +28,7 @@
 //  * Anything unusual (infeasible, empty, malformed, over/underflow) sets flags[b]; ctc_log.cu redoes exactly those
 //    utterances in the same stream with torch's inf / NaN / zero_infinity semantics.
 #include <cstdlib>
+#include <type_traits>
 
 #include "common.cuh"
 #include "ctc_params.cuh"
@@ -38,18 +39,20 @@ namespace {
 constexpr int KF = 8;                    // frames per chunk = renormalisation period = checkpoint period
 constexpr int E_EMPTY = -(1 << 20);      // exponent of a lane whose states are all zero
 constexpr int OFF = 50;                  // beta mantissas are kept 2^-OFF below 1 / (alpha mantissa)
-constexpr int CPMAX = 68;                // staged emission row: utterance h at [h*CPMAX, h*CPMAX + C], C <= 64
+constexpr int CPMAX = 64;                // staged emission row: utterance h at [h*CPMAX, +64): 32 banks x 2 levels
 constexpr int RW = 2 * CPMAX;
 constexpr unsigned FULL = 0xffffffffu;
+template <int N>
+using IC = std::integral_constant<int, N>;
 
 template <int NSL>
 struct PGeo {
     static constexpr int NL = NSL / 2;                     // label states per lane
     static constexpr int LCAP = 16 * NSL - 1;              // S = 2L+1 <= 32*NSL - 1
     static constexpr int U1OFF = ((LCAP + 3 + 3) & ~3) + 4;    // second utterance's sorted list inside a product row
-    static constexpr int ZERO = U1OFF - 1;                 // always 0
-    static constexpr int DUMP = U1OFF - 2;                 // swallows products of unused label slots
-    static constexpr int RS = ((U1OFF + LCAP + 3 - 4 + 31) / 32) * 32 + 4;   // product row stride, == 4 (mod 32)
+    static constexpr int RS = ((U1OFF + LCAP + 3 + 2 - 4 + 31) / 32) * 32 + 4;   // product row stride, == 4 (mod 32)
+    static constexpr int ZERO = RS - 1;                    // always 0 (past the sorted lists and the alpha row)
+    static constexpr int DUMP = RS - 2;                    // swallows products of unused label slots
     // mass can cross ceil(2*KF/NSL)+1 lane boundaries between two renormalisations, each multiplying the mantissa by
     // up to 2^GAP, plus 3^KF of growth: GAP * crossings + 14 < 126
     static constexpr int GAP = NSL == 2 ? 12 : NSL == 4 ? 22 : NSL == 8 ? 36 : 56;
@@ -85,21 +88,6 @@ __device__ __forceinline__ Cols make_cols(int lane, int C) {
     k.l0 = k.v0 ? k.c0 : 0;
     k.l1 = k.v1 ? k.c1 : 0;
     return k;
-}
-template <bool VEC>
-__device__ __forceinline__ float2 ld_row2(const float* __restrict__ src, const Cols& k) {
-    if constexpr (VEC) return __ldcs(reinterpret_cast<const float2*>(src + k.l0));
-    else return make_float2(__ldcs(src + k.l0), __ldcs(src + k.l1));
-}
-template <bool VEC>
-__device__ __forceinline__ void st_row2_smem(float* __restrict__ dst, const Cols& k, float2 v) {
-    if constexpr (VEC) { if (k.v0) *reinterpret_cast<float2*>(dst + k.c0) = v; }
-    else { if (k.v0) dst[k.c0] = v.x; if (k.v1) dst[k.c1] = v.y; }
-}
-template <bool VEC>
-__device__ __forceinline__ float2 ld_row2_smem(const float* __restrict__ src, const Cols& k) {
-    if constexpr (VEC) return *reinterpret_cast<const float2*>(src + k.l0);
-    else return make_float2(src[k.l0], src[k.l1]);
 }
 template <bool VEC>
 __device__ __forceinline__ void st_row2_gmem(float* __restrict__ dst, const Cols& k, float2 v) {
@@ -208,13 +196,13 @@ __host__ __device__ inline PairSmem pair_smem_layout(int NSL, int RS, bool regbu
     int o = 0;
     s.prod_off = o; o += KF * RS;                 // class-sorted label products -> prefix sums (setup scratch too)
     s.rows_off = o; o += KF * RW;                 // exp(lp) rows of the current chunk, both utterances
-    s.abuf_off = o; if (!regbuf) o += KF * (NSL / 2) * 64;    // alpha label states of the chunk (float2 per lane)
+    s.abuf_off = 0;                               // (!regbuf) alpha label states of frame r live in product row r
     s.total_floats = (o + 3) & ~3;
     return s;
 }
 
-template <int NSL, bool VEC, bool REGBUF>
-__global__ void __launch_bounds__(128)
+template <int NSL, bool VEC, bool REGBUF, int MAXR>
+__global__ void __maxnreg__(MAXR)
 ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     using G = PGeo<NSL>;
     constexpr int NL = G::NL, RS = G::RS, U1OFF = G::U1OFF, ZERO = G::ZERO, DUMP = G::DUMP, CKW = G::CKW;
@@ -228,7 +216,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     float* base = smem_f + (size_t)warp * lay.total_floats;
     float* prod = base + lay.prod_off;                           // [KF][RS]
     float* rows = base + lay.rows_off;                           // [KF][RW]
-    float2* abuf = reinterpret_cast<float2*>(base + lay.abuf_off);   // [KF][NL][32]
+    static_assert(REGBUF || PGeo<NSL>::RS >= 32 * NSL, "alpha label row must fit in a product row");
 
     const int C = p.C, blank = p.blank, T = p.T;
     const bool want_grad = p.grad != nullptr;
@@ -240,7 +228,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     int* lab = scratch;
     int* slot = scratch + 512;
     int* ctab = scratch + 1024;
-    static_assert(KF * (G::RS + RW) >= 1280, "setup scratch must fit in the product + emission rows");
+    static_assert(KF * (G::RS + RW) >= 1280 + 288, "setup scratch must fit in the product + emission rows");
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const int b = 2 * pair + h;
@@ -275,6 +263,64 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
 
     const Cols cols = make_cols<VEC>(lane, C);
 
+    // Emission layout.  The lattice gathers e[t][label] with one LDS per label state; with C > 32 classes a plain row
+    // makes two of the requested classes share a bank in almost every gather.  Per utterance, classes (and the zero
+    // that unused label slots read, item C) are therefore placed at position bank + 32*level such that two classes
+    // requested by the same gather instruction (same label slot q of different lanes) never share a bank: items are
+    // placed greedily, those present in most gather groups first, each into a bank whose residents are requested by
+    // none of its groups.
+    int* gm = scratch + 1280;                                    // [2][72] gather-group mask per item
+    int* cpos = scratch + 1280 + 144;                            // [2][72] position per item
+    for (int i = lane; i < 144; i += 32) gm[i] = 0;
+    __syncwarp();
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+#pragma unroll
+        for (int q = 0; q < NL; ++q) {
+            const int i = lane * NL + q;
+            atomicOr(&gm[h * 72 + (i < L[h] ? lab[h * 256 + i] : C)], 1 << q);
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        int G[3], posk[3];
+        bool valid[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int c = lane + 32 * k;
+            valid[k] = c <= C;
+            G[k] = valid[k] ? gm[h * 72 + c] : 0;
+            posk[k] = 0;
+        }
+        int bankmask = 0, cnt = 0;                               // lane = bank
+        for (int pass = 0; pass < 3; ++pass) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int pc = __popc(G[k]);
+                const bool sel = valid[k] && (pass == 0 ? pc >= 2 : pass == 1 ? pc == 1 : pc == 0);
+                unsigned m = __ballot_sync(FULL, sel);
+                while (m) {
+                    const int src = __ffs(m) - 1;
+                    m &= m - 1;
+                    const int gq = __shfl_sync(FULL, G[k], src);
+                    const bool ok = ((bankmask & gq) == 0) && cnt < 2;
+                    unsigned e = __ballot_sync(FULL, ok && cnt == 0);
+                    if (!e) e = __ballot_sync(FULL, ok);
+                    if (!e) e = __ballot_sync(FULL, cnt < 2);   // no conflict-free bank left: accept a conflict
+                    const int bsel = __ffs(e) - 1;
+                    const int pcur = __shfl_sync(FULL, cnt, bsel) * 32 + bsel;
+                    if (lane == bsel) { bankmask |= gq; ++cnt; }
+                    if (lane == src) posk[k] = pcur;
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            if (valid[k]) cpos[h * 72 + lane + 32 * k] = posk[k];
+    }
+    __syncwarp();
+
     // per-lane constants: emission pointers and skip masks of my label states
     const float* ep0[NL];
     const float* ep1[NL];
@@ -288,7 +334,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         for (int h = 0; h < 2; ++h) {
             const bool in = i < L[h];
             const int c = in ? lab[h * 256 + i] : -1;
-            eo[h] = in ? h * CPMAX + c : C;                      // rows[r][C] == 0
+            eo[h] = h * CPMAX + cpos[h * 72 + (in ? c : C)];     // item C: a slot that always holds 0
             am[h] = (in && i > 0 && lab[h * 256 + i - 1] != c) ? 1.f : 0.f;
             bm[h] = (in && i + 1 < L[h] && lab[h * 256 + i + 1] != c) ? 1.f : 0.f;
         }
@@ -297,8 +343,12 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         ma[q] = make_float2(am[0], am[1]);
         mb[q] = make_float2(bm[0], bm[1]);
     }
-    const float* bl0 = rows + blank;
-    const float* bl1 = rows + CPMAX + blank;
+    const float* bl0 = rows + cpos[blank];
+    const float* bl1 = rows + CPMAX + cpos[72 + blank];
+    // where my two columns of a log-prob row live in the staged row (w[2h+k]) and where the zero slots are
+    int wr[4];
+    wr[0] = cpos[cols.l0]; wr[1] = cpos[cols.l1]; wr[2] = CPMAX + cpos[72 + cols.l0]; wr[3] = CPMAX + cpos[72 + cols.l1];
+    const int zslot0 = cpos[C], zslot1 = CPMAX + cpos[72 + C];
 
     // class-sorted slots.  Label i of utterance h gets slot perm(i) of a list sorted by class (positions ascending
     // inside a class), cut at the class boundary nearest L/2 into two stretches; the second starts 16-byte aligned.
@@ -392,23 +442,31 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     __syncwarp();
     // zero pads of the staged rows (emission of unused label slots) and the ZERO slot of the product rows
     if (lane < KF) {
-        for (int c = C; c < CPMAX; ++c) rows[lane * RW + c] = 0.f;
-        for (int c = C; c < CPMAX; ++c) rows[lane * RW + CPMAX + c] = 0.f;
+        rows[lane * RW + zslot0] = 0.f;
+        rows[lane * RW + zslot1] = 0.f;
         prod[lane * RS + ZERO] = 0.f;
     }
     __syncwarp();
 
     // ------------------------------------------------------------------------------------------ geometry
+    // Chunks are either full (KF frames) or single frames (the remainders of the two phases), so that every chunk
+    // body is straight-line code: joint phase [0, Tmin), then the longer utterance alone [Tmin, Tmax).
     const int Tmin = min(Tb[0], Tb[1]), Tmax = max(Tb[0], Tb[1]);
-    const int nJ = (Tmin + KF - 1) / KF, nch = nJ + (Tmax - Tmin + KF - 1) / KF;
-    auto chunk_geom = [&](int j, int& t0, int& n) {
-        if (j < nJ) { t0 = j * KF; n = min(KF, Tmin - t0); }
-        else { t0 = Tmin + (j - nJ) * KF; n = min(KF, Tmax - t0); }
+    const int nJ8 = Tmin / KF, cJ = nJ8 + Tmin % KF;
+    const int nS8 = (Tmax - Tmin) / KF, cS = cJ + nS8;
+    const int nch = cS + (Tmax - Tmin) % KF;
+    auto chunk_geom = [&](int j, int& t0) -> bool {               // true: full chunk
+        if (j < nJ8) { t0 = j * KF; return true; }
+        if (j < cJ) { t0 = nJ8 * KF + (j - nJ8); return false; }
+        if (j < cS) { t0 = Tmin + (j - cJ) * KF; return true; }
+        t0 = Tmin + nS8 * KF + (j - cS);
+        return false;
     };
     // rows are always read from a live utterance's memory; an idle half re-reads its partner's rows
     const int bsrc0 = act[0] ? bidx[0] : bidx[1], bsrc1 = act[1] ? bidx[1] : bidx[0];
-    const float* lp0 = p.lp + (size_t)bsrc0 * p.stride_b;
-    const float* lp1 = p.lp + (size_t)bsrc1 * p.stride_b;
+    const float* lp0 = p.lp + (size_t)bsrc0 * p.stride_b + cols.l0;
+    const float* lp1 = p.lp + (size_t)bsrc1 * p.stride_b + cols.l0;
+    const int dl1 = cols.l1 - cols.l0;
     const size_t gstride = (size_t)p.B * C;
     float* gr0 = want_grad ? p.grad + (size_t)bidx[0] * C : nullptr;
     float* gr1 = want_grad ? p.grad + (size_t)bidx[1] * C : nullptr;
@@ -417,27 +475,50 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     for (int h = 0; h < 2; ++h) g[h] = act[h] ? (p.grad_out ? p.grad_out[bidx[h]] : 1.f) * p.gscalar : 0.f;
 
     float2 pre0[KF], pre1[KF];                          // the next chunk's rows, in flight
-    auto load_rows = [&](int j) {                       // rows past the end of a partial chunk re-read its last row
-        int t0, n;
-        chunk_geom(j, t0, n);
+    auto load_rows = [&](auto nfc, int t0) {
+        constexpr int NF = decltype(nfc)::value;
         const float* s0 = lp0 + (size_t)t0 * p.stride_t;
         const float* s1 = lp1 + (size_t)t0 * p.stride_t;
 #pragma unroll
-        for (int r = 0; r < KF; ++r) {
-            const size_t o = (size_t)min(r, n - 1) * p.stride_t;
-            pre0[r] = ld_row2<VEC>(s0 + o, cols);
-            pre1[r] = ld_row2<VEC>(s1 + o, cols);
+        for (int r = 0; r < NF; ++r) {
+            if constexpr (VEC) {
+                pre0[r] = __ldcs(reinterpret_cast<const float2*>(s0));
+                pre1[r] = __ldcs(reinterpret_cast<const float2*>(s1));
+            } else {
+                pre0[r] = make_float2(__ldcs(s0), __ldcs(s0 + dl1));
+                pre1[r] = make_float2(__ldcs(s1), __ldcs(s1 + dl1));
+            }
+            s0 += p.stride_t;
+            s1 += p.stride_t;
         }
     };
-    auto commit_rows = [&](bool kill0, bool kill1) {    // p = exp(lp) into shared memory; an idle half emits zeros
+    auto load_chunk = [&](int j) {
+        int t0;
+        if (chunk_geom(j, t0)) load_rows(IC<KF>{}, t0);
+        else load_rows(IC<1>{}, t0);
+    };
+    auto put_row = [&](int r, float2 v0, float2 v1) {
+        float* d = rows + r * RW;
+        if (cols.v0) { d[wr[0]] = v0.x; d[wr[2]] = v1.x; }
+        if (cols.v1) { d[wr[1]] = v0.y; d[wr[3]] = v1.y; }
+    };
+    auto commit_rows = [&](auto nfc, bool kill0, bool kill1) {   // p = exp(lp) into shared memory; an idle half emits zeros
+        constexpr int NF = decltype(nfc)::value;
+        if (kill0 || kill1) {
 #pragma unroll
-        for (int r = 0; r < KF; ++r) {
-            float2 v0 = make_float2(fast_exp(pre0[r].x), fast_exp(pre0[r].y));
-            float2 v1 = make_float2(fast_exp(pre1[r].x), fast_exp(pre1[r].y));
-            if (kill0) v0 = make_float2(0.f, 0.f);
-            if (kill1) v1 = make_float2(0.f, 0.f);
-            st_row2_smem<VEC>(rows + r * RW, cols, v0);
-            st_row2_smem<VEC>(rows + r * RW + CPMAX, cols, v1);
+            for (int r = 0; r < NF; ++r) {
+                float2 v0 = make_float2(fast_exp(pre0[r].x), fast_exp(pre0[r].y));
+                float2 v1 = make_float2(fast_exp(pre1[r].x), fast_exp(pre1[r].y));
+                if (kill0) v0 = make_float2(0.f, 0.f);
+                if (kill1) v1 = make_float2(0.f, 0.f);
+                put_row(r, v0, v1);
+            }
+        } else {
+#pragma unroll
+            for (int r = 0; r < NF; ++r) {
+                put_row(r, make_float2(fast_exp(pre0[r].x), fast_exp(pre0[r].y)),
+                        make_float2(fast_exp(pre1[r].x), fast_exp(pre1[r].y)));
+            }
         }
     };
 
@@ -453,7 +534,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     int koff[2] = {0, 0};
     float* ck = ckpt_ws + (size_t)pair * n_ckpt * CKW;
 
-    load_rows(0);
+    load_chunk(0);
     if (want_grad) {                                    // rows t >= T_max of the gradient are zero (torch semantics)
         for (int t = Tmax; t < T; ++t) {
             if (act[0]) st_row2_gmem<VEC>(gr0 + (size_t)t * gstride, cols, make_float2(0.f, 0.f));
@@ -461,14 +542,13 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         }
     }
 
-    for (int j = 0; j < nch; ++j) {
-        int t0, n;
-        chunk_geom(j, t0, n);
+    auto fwd_chunk = [&](auto nfc, int j, int t0) {
+        constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
         __syncwarp();
-        commit_rows(kill0, kill1);
+        commit_rows(nfc, kill0, kill1);
         __syncwarp();
-        if (j + 1 < nch) load_rows(j + 1);
+        if (j + 1 < nch) load_chunk(j + 1);
         {
             bool ok[2];
             renorm_alpha<NSL>(a, ea, sca, lane, ok);
@@ -483,9 +563,8 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             reinterpret_cast<int2*>(c + 64 * NSL)[lane] = make_int2(ea[0], ea[1]);
         }
 #pragma unroll
-        for (int r = 0; r < KF; ++r)
-            if (r < n) alpha_step<NSL>(a, sca, r * RW, bl0, bl1, ep0, ep1, ma);
-        const int tend = t0 + n;
+        for (int r = 0; r < NF; ++r) alpha_step<NSL>(a, sca, r * RW, bl0, bl1, ep0, ep1, ma);
+        const int tend = t0 + NF;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             if (act[h] && tend == Tb[h]) {
@@ -512,6 +591,11 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 }
             }
         }
+    };
+    for (int j = 0; j < nch; ++j) {
+        int t0;
+        if (chunk_geom(j, t0)) fwd_chunk(IC<KF>{}, j, t0);
+        else fwd_chunk(IC<1>{}, j, t0);
     }
     if (!want_grad || ((flag[0] || !act[0]) && (flag[1] || !act[1]))) {
 #pragma unroll
@@ -528,40 +612,40 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     float cst[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) cst[k] = isblank[k] ? zc[k >> 1] : 0.f;
-    // scan role of this lane: frame f, utterance sh, stretch part
+    // scan role of this lane: frame sf, utterance sh, stretch spart
     const int sf = lane & (KF - 1), sh = (lane >> 3) & 1, spart = lane >> 4;
     const int s_split = sh ? st_split[1] : st_split[0], s_pad = sh ? st_pad[1] : st_pad[0], s_L = sh ? L[1] : L[0];
     const int kb = sh * U1OFF + (spart ? s_split + s_pad : 0);
     const int ke = sh * U1OFF + (spart ? s_L + s_pad : s_split);
     int bad_occ = 0;
 
-    if (nch >= 2) load_rows(nch - 2);
-    for (int j = nch - 1; j >= 0; --j) {
-        int t0, n;
-        chunk_geom(j, t0, n);
+    auto load_ckpt = [&](int j) {                       // alpha entering chunk j (post-renormalisation) + exponents
+        const float* c = ck + (size_t)j * CKW;
+#pragma unroll
+        for (int q = 0; q < NSL / 2; ++q) {
+            const float4 v = reinterpret_cast<const float4*>(c)[q * 32 + lane];
+            a[2 * q] = make_float2(v.x, v.y);
+            a[2 * q + 1] = make_float2(v.z, v.w);
+        }
+        const int2 e2 = reinterpret_cast<const int2*>(c + 64 * NSL)[lane];
+        ea[0] = e2.x; ea[1] = e2.y;
+    };
+
+    auto bwd_chunk = [&](auto nfc, int j, int t0) {
+        constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
+        load_ckpt(j);
         if (j < nch - 1) {                              // the last chunk is still staged (and exponentiated)
             __syncwarp();
-            commit_rows(kill0, kill1);
+            commit_rows(nfc, kill0, kill1);
             __syncwarp();
-            if (j > 0) load_rows(j - 1);
+            if (j > 0) load_chunk(j - 1);
         }
-        // alpha entering the chunk (post-renormalisation) and the exponents that go with it
-        {
-            const float* c = ck + (size_t)j * CKW;
-#pragma unroll
-            for (int q = 0; q < NSL / 2; ++q) {
-                const float4 v = reinterpret_cast<const float4*>(c)[q * 32 + lane];
-                a[2 * q] = make_float2(v.x, v.y);
-                a[2 * q + 1] = make_float2(v.z, v.w);
-            }
-            const int2 e2 = reinterpret_cast<const int2*>(c + 64 * NSL)[lane];
-            ea[0] = e2.x; ea[1] = e2.y;
-        }
+        // a / ea hold the checkpoint of this chunk: boundary factors and the beta exponents that go with it
         float2 scb;
         {
             float fb[2], sa[2], sb[2], ini[2];
-            const int tend = t0 + n;
+            const int tend = t0 + NF;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int el = __shfl_up_sync(FULL, ea[h], 1), er = __shfl_down_sync(FULL, ea[h], 1);
@@ -571,9 +655,10 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 const bool starts = act[h] && tend == Tb[h];             // beta_T enters here
                 fb[h] = starts ? 0.f : pow2i(eb[h] - ebn);
                 ini[h] = starts ? pow2i(-ebn) : 0.f;
-                // beta_T = 1 must be representable in the lane that owns state S-1
-                const bool owner = (S[h] - 1) / NSL == lane;
-                if (__any_sync(FULL, starts && owner && (ebn > 120 || ebn < -120)) && !flag[h]) flag[h] = 6;
+                if (starts) {                            // beta_T = 1 must be representable in the lane that owns S-1
+                    const bool owner = (S[h] - 1) / NSL == lane;
+                    if (__any_sync(FULL, owner && (ebn > 120 || ebn < -120)) && !flag[h]) flag[h] = 6;
+                }
                 eb[h] = ebn;
             }
             sca = make_float2(sa[0], sa[1]);
@@ -588,39 +673,44 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             }
         }
         // recompute alpha over the chunk, keeping the label states
-        float2 A[REGBUF ? KF : 1][NL];
+        float2 A[REGBUF ? NF : 1][NL];
 #pragma unroll
-        for (int r = 0; r < KF; ++r) {
-            if (r < n) {
-                alpha_step<NSL>(a, sca, r * RW, bl0, bl1, ep0, ep1, ma);
+        for (int r = 0; r < NF; ++r) {
+            alpha_step<NSL>(a, sca, r * RW, bl0, bl1, ep0, ep1, ma);
 #pragma unroll
-                for (int q = 0; q < NL; ++q) {
-                    if constexpr (REGBUF) A[r][q] = a[2 * q + 1];
-                    else abuf[(r * NL + q) * 32 + lane] = a[2 * q + 1];
-                }
+            for (int q = 0; q < NL; ++q) {
+                if constexpr (REGBUF) A[r][q] = a[2 * q + 1];
+                else reinterpret_cast<float2*>(prod + r * RS)[q * 32 + lane] = a[2 * q + 1];
             }
+        }
+        if (j > 0) {                                    // pull the next chunk's checkpoint into L2 meanwhile
+            const float* c = ck + (size_t)(j - 1) * CKW;
+#pragma unroll
+            for (int q = 0; q < NSL / 2; ++q) asm volatile("prefetch.global.L2 [%0];" ::"l"(c + (q * 32 + lane) * 4));
+            if (lane < 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(c + 64 * NSL + lane * 32));
         }
         __syncwarp();                                   // the previous chunk's gradient rows have been read
         // beta over the chunk; label products alpha_t(s) * u_t(s) into their class-sorted slots
 #pragma unroll
-        for (int r = KF - 1; r >= 0; --r) {
-            if (r < n) {
-                float2 ul[NL];
-                beta_step<NSL>(bt, ul, scb, r * RW, bl0, bl1, ep0, ep1, mb);
+        for (int r = NF - 1; r >= 0; --r) {
+            float2 ul[NL], al[NL];
 #pragma unroll
-                for (int q = 0; q < NL; ++q) {
-                    float2 al;
-                    if constexpr (REGBUF) al = A[r][q];
-                    else al = abuf[(r * NL + q) * 32 + lane];
-                    const float2 pl = __fmul2_rn(al, ul[q]);
-                    pp0[q][r * RS] = pl.x;
-                    pp1[q][r * RS] = pl.y;
-                }
+            for (int q = 0; q < NL; ++q) {
+                if constexpr (REGBUF) al[q] = A[r][q];
+                else al[q] = reinterpret_cast<const float2*>(prod + r * RS)[q * 32 + lane];
+            }
+            beta_step<NSL>(bt, ul, scb, r * RW, bl0, bl1, ep0, ep1, mb);
+            if constexpr (!REGBUF) __syncwarp();          // every lane has read its alpha before the row is reused
+#pragma unroll
+            for (int q = 0; q < NL; ++q) {
+                const float2 pl = __fmul2_rn(al[q], ul[q]);
+                pp0[q][r * RS] = pl.x;
+                pp1[q][r * RS] = pl.y;
             }
         }
         __syncwarp();
         // in-place prefix sums of the sorted products: lane = (frame, utterance, stretch)
-        if (sf < n) {
+        if (sf < NF) {
             float* pr = prod + sf * RS;
             float acc = 0.f;
             for (int k = kb; k < ke; k += 4) {
@@ -637,25 +727,34 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         {
             const float g0 = kill0 ? 0.f : g[0], g1 = kill1 ? 0.f : g[1];
             const float zg0 = zi[0] * g0, zg1 = zi[1] * g1;
+            const float lim0 = kill0 ? -3.0e38f : -1e-3f * zc[0], lim1 = kill1 ? -3.0e38f : -1e-3f * zc[1];
+            float* w0 = gr0 + (size_t)t0 * gstride;
+            float* w1 = gr1 + (size_t)t0 * gstride;
 #pragma unroll
-            for (int r = 0; r < KF; ++r) {
-                if (r < n) {
-                    const float2 pv0 = ld_row2_smem<VEC>(rows + r * RW, cols);
-                    const float2 pv1 = ld_row2_smem<VEC>(rows + r * RW + CPMAX, cols);
-                    float o[4];
+            for (int r = 0; r < NF; ++r) {
+                const float* d = rows + r * RW;
+                const float2 pv0 = make_float2(d[wr[0]], d[wr[1]]), pv1 = make_float2(d[wr[2]], d[wr[3]]);
+                float o[4];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) o[k] = fmaf(sg[k], pli[k][r * RS], cst[k]) - plj[k][r * RS];
-                    // every occupancy must be a number >= 0 up to rounding: catches overflow / NaN anywhere upstream
-                    if (!(o[0] >= -1e-3f * zc[0]) || !(o[1] >= -1e-3f * zc[0])) bad_occ |= kill0 ? 0 : 1;
-                    if (!(o[2] >= -1e-3f * zc[1]) || !(o[3] >= -1e-3f * zc[1])) bad_occ |= kill1 ? 0 : 2;
-                    const size_t go = (size_t)(t0 + r) * gstride;
-                    if (act[0])
-                        st_row2_gmem<VEC>(gr0 + go, cols, make_float2(fmaf(-o[0], zg0, pv0.x * g0), fmaf(-o[1], zg0, pv0.y * g0)));
-                    if (act[1])
-                        st_row2_gmem<VEC>(gr1 + go, cols, make_float2(fmaf(-o[2], zg1, pv1.x * g1), fmaf(-o[3], zg1, pv1.y * g1)));
-                }
+                for (int k = 0; k < 4; ++k) o[k] = fmaf(sg[k], pli[k][r * RS], cst[k]) - plj[k][r * RS];
+                // every occupancy must be a number >= 0 up to rounding: catches overflow / NaN anywhere upstream
+                if (!(fminf(o[0], o[1]) >= lim0)) bad_occ |= 1;
+                if (!(fminf(o[2], o[3]) >= lim1)) bad_occ |= 2;
+                if (act[0])
+                    st_row2_gmem<VEC>(w0, cols, make_float2(fmaf(-o[0], zg0, pv0.x * g0), fmaf(-o[1], zg0, pv0.y * g0)));
+                if (act[1])
+                    st_row2_gmem<VEC>(w1, cols, make_float2(fmaf(-o[2], zg1, pv1.x * g1), fmaf(-o[3], zg1, pv1.y * g1)));
+                w0 += gstride;
+                w1 += gstride;
             }
         }
+    };
+
+    if (nch >= 2) load_chunk(nch - 2);
+    for (int j = nch - 1; j >= 0; --j) {
+        int t0;
+        if (chunk_geom(j, t0)) bwd_chunk(IC<KF>{}, j, t0);
+        else bwd_chunk(IC<1>{}, j, t0);
     }
     {   // beta must have stayed finite to the very first frame (a blank state's overflow shows nowhere else)
 #pragma unroll
@@ -685,28 +784,39 @@ int env_int(const char* name, int dflt) {
     return e ? atoi(e) : dflt;
 }
 
-template <int NSL, bool VEC, bool REGBUF>
+template <int NSL, bool VEC, bool REGBUF, int MAXR>
 int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
     const PairSmem lay = pair_smem_layout(NSL, PGeo<NSL>::RS, REGBUF);
-    const size_t per_warp = (size_t)lay.total_floats * 4;
+    size_t smem = (size_t)lay.total_floats * 4;                  // one warp (= one pair) per CTA
     const int npairs = (p.B + 1) / 2;
-    static int wpc_env = env_int("MDD_CTC_PAIR_WPC", 2);
-    int warps = wpc_env < 1 ? 1 : wpc_env > 4 ? 4 : wpc_env;
-    const int spread = (npairs + kNumSM - 1) / kNumSM;           // small batches: one warp per SM first
-    if (warps > spread) warps = spread > 0 ? spread : 1;
-    const size_t smem = per_warp * warps;
-    static bool configured = false;
-    if (!configured) {
-        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, VEC, REGBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)(per_warp * 4)) != cudaSuccess) {
+    // Warps per SM: the register file allows 8; fewer when that packs the pairs into full waves (a pair runs for the
+    // whole kernel, so 13.8 pairs per SM are better served by 7 warps x 2 waves than by 8 + 5.8).
+    static int wps_env = env_int("MDD_CTC_PAIR_WPS", 0);
+    int wps = wps_env;
+    if (wps <= 0) {
+        double best = 0.0;
+        const int wmax = MAXR >= 255 ? 8 : MAXR >= 168 ? 12 : MAXR >= 144 ? 14 : 16;
+        for (int w = wmax; w >= wmax - 2; --w) {
+            const long long slots = (long long)kNumSM * w;
+            const double eff = (double)npairs / (double)(((npairs + slots - 1) / slots) * slots);
+            if (eff > best + 0.04) { best = eff; wps = w; }
+        }
+    }
+    if (wps > 0 && wps < 32) {
+        const size_t want = ((233472 / (size_t)wps) - 1024 - 64) & ~(size_t)15;
+        if (want > smem && want <= 227 * 1024) smem = want;
+    }
+    static size_t configured = 0;
+    if (configured < smem) {
+        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, VEC, REGBUF, MAXR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem) != cudaSuccess) {
             cudaGetLastError();
             return MDD_E_CUDA;
         }
-        configured = true;
+        configured = smem;
     }
-    const int n_ckpt = (p.T + KF - 1) / KF + 2;
-    const int grid = (npairs + warps - 1) / warps;
-    ctc_pair_kernel<NSL, VEC, REGBUF><<<grid, warps * 32, smem, st>>>(p, ws, n_ckpt);
+    const int n_ckpt = p.T / KF + 2 * KF;
+    ctc_pair_kernel<NSL, VEC, REGBUF, MAXR><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
     MDD_CHECK_LAUNCH();
     return MDD_OK;
 }
@@ -715,29 +825,39 @@ template <int NSL>
 int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
     const bool vec = (p.C % 2 == 0) && (p.stride_t % 2 == 0) && (p.stride_b % 2 == 0) && ((uintptr_t)p.lp % 8 == 0) &&
                      (!p.grad || (uintptr_t)p.grad % 8 == 0);
-    static int regbuf = env_int("MDD_CTC_PAIR_REGBUF", 1);
-    if (regbuf) return vec ? launch_cfg<NSL, true, true>(p, ws, st) : launch_cfg<NSL, false, true>(p, ws, st);
-    return vec ? launch_cfg<NSL, true, false>(p, ws, st) : launch_cfg<NSL, false, false>(p, ws, st);
+    if constexpr (NSL == 8) {
+        static int regbuf = env_int("MDD_CTC_PAIR_REGBUF", 1), maxr = env_int("MDD_CTC_PAIR_MAXR", 255);
+        if (vec) {
+            if (regbuf) return launch_cfg<NSL, true, true, 255>(p, ws, st);
+            if (maxr >= 255) return launch_cfg<NSL, true, false, 255>(p, ws, st);
+            if (maxr >= 168) return launch_cfg<NSL, true, false, 168>(p, ws, st);
+            if (maxr >= 144) return launch_cfg<NSL, true, false, 144>(p, ws, st);
+            return launch_cfg<NSL, true, false, 128>(p, ws, st);
+        }
+    }
+    return vec ? launch_cfg<NSL, true, false, 168>(p, ws, st) : launch_cfg<NSL, false, false, 168>(p, ws, st);
 }
 
 }  // namespace
 
-bool ctc_pair_supported(int C, int Lmax) { return C <= 64 && pick_nsl(Lmax) != 0; }
+bool ctc_pair_supported(int C, int Lmax) { return C <= 63 && pick_nsl(Lmax) != 0; }   // C classes + the zero item <= 64 slots
 
 size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
     const int nsl = pick_nsl(Lmax);
     if (!nsl) return 0;
-    const size_t n_ckpt = (size_t)(T + KF - 1) / KF + 2;
+    const size_t n_ckpt = (size_t)T / KF + 2 * KF;
     return (size_t)((B + 1) / 2) * n_ckpt * 32 * (2 * nsl + 2) * 4;
 }
 
 int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st) {
     float* w = reinterpret_cast<float*>(ws);
     switch (pick_nsl(p.Lmax)) {
+#ifndef MDD_PAIR_ONLY8
         case 2: return launch_nsl<2>(p, w, st);
         case 4: return launch_nsl<4>(p, w, st);
-        case 8: return launch_nsl<8>(p, w, st);
         case 16: return launch_nsl<16>(p, w, st);
+#endif
+        case 8: return launch_nsl<8>(p, w, st);
         default: return MDD_E_UNSUPPORTED;
     }
 }

@@ -88,6 +88,15 @@ def ctc_loss_raw(log_probs, targets, input_lengths, target_lengths, blank=0, zer
     return nll, (grad if want_grad else None), status
 
 
+def last_fallback_flags(B, dev=None):
+    """Diagnostics: the per-utterance flags the last mdd_ctc_loss call on this device left in its workspace
+    (0 = the packed linear-domain kernel produced the result, otherwise the log-space kernel redid the utterance)."""
+    dev = _rt.device() if dev is None else dev
+    ws = _rt._ws_cache[(dev.index, "ctc")]
+    off = (B * 8 + 255) // 256 * 256
+    return ws[off:off + 4 * B].view(torch.int32).clone()
+
+
 class _CTCLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, log_probs, targets, input_lengths, target_lengths, blank, zero_infinity, algo, validate):

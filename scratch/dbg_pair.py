@@ -17,7 +17,7 @@ def case(T,B,C,L, il=None, tl=None, tg=None, tag=""):
     flags = ws[off:off+B*4].view(torch.int32).cpu().tolist()
     d = (g1-g2).abs()
     per = d.amax(dim=(0,2)).cpu()
-    print(tag, (T,B,C,L), 'flags', [(f&255, f>>8) for f in flags if f][:6], 'nll rel %.2e' % float(((n1-n2)/n1).abs().max()), 'grad diff %.3e' % float(d.max()), 'nan', int(torch.isnan(g2).sum()))
+    print(tag, (T,B,C,L), 'NFLAGGED', sum(1 for f in flags if f), [(f&255, f>>8) for f in flags if f][:6], 'nll rel %.2e' % float(((n1-n2)/n1).abs().max()), 'grad diff %.3e' % float(d.max()), 'nan', int(torch.isnan(g2).sum()))
     for b in range(B):
         if per[b] > 1e-4 or per[b] != per[b]:
             idx = (d[:,b,:] > 1e-4).nonzero().cpu()
