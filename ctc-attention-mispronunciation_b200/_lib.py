@@ -60,7 +60,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(src), hdr_t):
             continue
         log = open(obj + ".log", "w")
-        procs.append((src, log, subprocess.Popen([nvcc] + NVCC_FLAGS + ["-c", src, "-o", obj], stdout=log,
+        extra = os.environ.get("MDD_NVCC_EXTRA", "").split()          # e.g. -DMDD_PAIR_TIMING for a debug build
+        procs.append((src, log, subprocess.Popen([nvcc] + NVCC_FLAGS + extra + ["-c", src, "-o", obj], stdout=log,
                                                  stderr=subprocess.STDOUT)))
     failed = []
     for src, log, pr in procs:

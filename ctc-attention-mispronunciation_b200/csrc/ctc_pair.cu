@@ -45,6 +45,17 @@ constexpr unsigned FULL = 0xffffffffu;
 template <int N>
 using IC = std::integral_constant<int, N>;
 
+#ifdef MDD_PAIR_TIMING
+__device__ unsigned long long g_phase_cycles[16];
+#define PT_DECL long long pt_last = clock64(); long long pt_acc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+#define PT(i) { asm volatile("" ::: "memory"); const long long pt_now = clock64(); pt_acc[i] += pt_now - pt_last; pt_last = pt_now; }
+#define PT_FLUSH if (lane == 0) { for (int i = 0; i < 12; ++i) atomicAdd(&g_phase_cycles[i], (unsigned long long)pt_acc[i]); }
+#else
+#define PT_DECL
+#define PT(i)
+#define PT_FLUSH
+#endif
+
 template <int NSL>
 struct PGeo {
     static constexpr int NL = NSL / 2;                     // label states per lane
@@ -280,6 +291,9 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             const int i = lane * NL + q;
             atomicOr(&gm[h * 72 + (i < L[h] ? lab[h * 256 + i] : C)], 1 << q);
         }
+        // the row commit / read-back accesses: all first columns of the lanes together, all second columns together
+        if (cols.v0) atomicOr(&gm[h * 72 + cols.c0], 1 << NL);
+        if (cols.v1) atomicOr(&gm[h * 72 + cols.c1], 1 << (NL + 1));
     }
     __syncwarp();
 #pragma unroll
@@ -358,6 +372,8 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     const float* plj[4];
     float sg[4];
     bool isblank[4];
+    float chain_m[2] = {0.f, 0.f};
+    const bool chain = VEC && blank == 0;                        // P[pe(c1)] is P[E(c0)] or 0: three lookups, not four
     int st_split[2], st_pad[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -426,12 +442,14 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 if (split > 0) oi = h * U1OFF + split - 1;
                 if (Lh > split) oj = h * U1OFF + Lh + pad - 1;
             } else if (valid) {
+                // E = last slot of the class (of the nearest present class below it if the class is absent),
+                // pe = slot before its first element (ZERO at the head of a stretch; = E for an absent class)
                 const int st = ctab[h * 128 + c], n = ctab[h * 128 + 64 + c];
-                if (n > 0) {
-                    const int stp = st + (st >= split ? pad : 0);
-                    oi = h * U1OFF + stp + n - 1;
-                    if (!(st == 0 || st == split)) oj = h * U1OFF + stp - 1;
-                }
+                auto slotpos = [&](int sp) { return h * U1OFF + sp + (sp >= split ? pad : 0); };
+                if (st + n > 0) oi = slotpos(st + n - 1);
+                if (n == 0) oj = oi;
+                else if (!(st == 0 || st == split)) oj = slotpos(st - 1);
+                if (k == 1) chain_m[h] = (oj == ZERO) ? 0.f : 1.f;    // second column continues the first one's prefix
             }
             pli[2 * h + k] = prod + oi;
             plj[2 * h + k] = prod + oj;
@@ -534,6 +552,8 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     int koff[2] = {0, 0};
     float* ck = ckpt_ws + (size_t)pair * n_ckpt * CKW;
 
+    PT_DECL
+    PT(0)                                               // setup
     load_chunk(0);
     if (want_grad) {                                    // rows t >= T_max of the gradient are zero (torch semantics)
         for (int t = Tmax; t < T; ++t) {
@@ -545,16 +565,35 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     auto fwd_chunk = [&](auto nfc, int j, int t0) {
         constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
+#ifdef MDD_PAIR_TIMING
+        PT(2)
+        asm volatile("" ::"f"(pre0[0].x), "f"(pre1[NF - 1].y));
+        PT(11)                                          // fwd: waiting for the rows
+#endif
         __syncwarp();
         commit_rows(nfc, kill0, kill1);
         __syncwarp();
+        PT(8)                                           // fwd: commit
         if (j + 1 < nch) load_chunk(j + 1);
+        if constexpr (NF == KF) {                       // rows two chunks ahead -> L2 (the next chunk's are in flight)
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const int idx = lane + 32 * k;          // 48 tasks: row, utterance, 128-byte part of its 4*C bytes
+                const int r = idx / 6, u = (idx % 6) / 3, part = idx % 3;
+                const int t = t0 + 2 * KF + r;
+                if (idx < 6 * KF && t < Tmax) {
+                    const float* q = (u ? lp1 : lp0) - cols.l0 + (size_t)t * p.stride_t + min(part * 32, C - 1);
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+                }
+            }
+        }
         {
             bool ok[2];
             renorm_alpha<NSL>(a, ea, sca, lane, ok);
             if (!ok[0] && !kill0 && !flag[0]) flag[0] = 2 | (t0 << 8);
             if (!ok[1] && !kill1 && !flag[1]) flag[1] = 2 | (t0 << 8);
         }
+        PT(1)                                           // fwd: commit, prefetch, renormalisation
         if (want_grad) {                                // alpha entering chunk j, after its renormalisation
             float* c = ck + (size_t)j * CKW;
 #pragma unroll
@@ -564,6 +603,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         }
 #pragma unroll
         for (int r = 0; r < NF; ++r) alpha_step<NSL>(a, sca, r * RW, bl0, bl1, ep0, ep1, ma);
+        PT(2)                                           // fwd: checkpoint store + alpha steps
         const int tend = t0 + NF;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -619,28 +659,33 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     const int ke = sh * U1OFF + (spart ? s_L + s_pad : s_split);
     int bad_occ = 0;
 
-    auto load_ckpt = [&](int j) {                       // alpha entering chunk j (post-renormalisation) + exponents
+    // alpha entering chunk j (post-renormalisation) + exponents.  Volatile asm: the loads are issued where they are
+    // written (right after the previous chunk's alpha recomputation), so their latency hides behind beta / scan / rows.
+    auto load_ckpt = [&](int j) {
         const float* c = ck + (size_t)j * CKW;
 #pragma unroll
         for (int q = 0; q < NSL / 2; ++q) {
-            const float4 v = reinterpret_cast<const float4*>(c)[q * 32 + lane];
-            a[2 * q] = make_float2(v.x, v.y);
-            a[2 * q + 1] = make_float2(v.z, v.w);
+            asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(a[2 * q].x), "=f"(a[2 * q].y), "=f"(a[2 * q + 1].x), "=f"(a[2 * q + 1].y)
+                         : "l"(c + (q * 32 + lane) * 4));
         }
-        const int2 e2 = reinterpret_cast<const int2*>(c + 64 * NSL)[lane];
-        ea[0] = e2.x; ea[1] = e2.y;
+        asm volatile("ld.global.v2.s32 {%0, %1}, [%2];" : "=r"(ea[0]), "=r"(ea[1]) : "l"(c + 64 * NSL + lane * 2));
     };
 
     auto bwd_chunk = [&](auto nfc, int j, int t0) {
         constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
-        load_ckpt(j);
         if (j < nch - 1) {                              // the last chunk is still staged (and exponentiated)
             __syncwarp();
             commit_rows(nfc, kill0, kill1);
             __syncwarp();
             if (j > 0) load_chunk(j - 1);
         }
+        PT(9)                                           // bwd: commit + row loads
+#ifdef MDD_PAIR_TIMING
+        asm volatile("" ::"r"(ea[0]), "r"(ea[1]), "f"(a[0].x), "f"(a[NSL - 1].y));
+        PT(10)                                          // bwd: waiting for the checkpoint
+#endif
         // a / ea hold the checkpoint of this chunk: boundary factors and the beta exponents that go with it
         float2 scb;
         {
@@ -672,6 +717,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 if (s == S[1] - 1) bt[jj].y += ini[1];
             }
         }
+        PT(3)                                           // bwd: commit, prefetch, exponent bookkeeping
         // recompute alpha over the chunk, keeping the label states
         float2 A[REGBUF ? NF : 1][NL];
 #pragma unroll
@@ -683,13 +729,8 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 else reinterpret_cast<float2*>(prod + r * RS)[q * 32 + lane] = a[2 * q + 1];
             }
         }
-        if (j > 0) {                                    // pull the next chunk's checkpoint into L2 meanwhile
-            const float* c = ck + (size_t)(j - 1) * CKW;
-#pragma unroll
-            for (int q = 0; q < NSL / 2; ++q) asm volatile("prefetch.global.L2 [%0];" ::"l"(c + (q * 32 + lane) * 4));
-            if (lane < 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(c + 64 * NSL + lane * 32));
-        }
         __syncwarp();                                   // the previous chunk's gradient rows have been read
+        PT(4)                                           // bwd: alpha recomputation
         // beta over the chunk; label products alpha_t(s) * u_t(s) into their class-sorted slots
 #pragma unroll
         for (int r = NF - 1; r >= 0; --r) {
@@ -708,7 +749,9 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 pp1[q][r * RS] = pl.y;
             }
         }
+        if (j > 0) load_ckpt(j - 1);                    // the alpha buffer is dead: the next checkpoint travels meanwhile
         __syncwarp();
+        PT(5)                                           // bwd: beta + product scatter
         // in-place prefix sums of the sorted products: lane = (frame, utterance, stretch)
         if (sf < NF) {
             float* pr = prod + sf * RS;
@@ -723,6 +766,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             }
         }
         __syncwarp();
+        PT(6)                                           // bwd: prefix sums
         // gradient rows of the chunk: (softmax prob - occupancy / Z) * g
         {
             const float g0 = kill0 ? 0.f : g[0], g1 = kill1 ? 0.f : g[1];
@@ -735,8 +779,16 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 const float* d = rows + r * RW;
                 const float2 pv0 = make_float2(d[wr[0]], d[wr[1]]), pv1 = make_float2(d[wr[2]], d[wr[3]]);
                 float o[4];
+                if (chain) {
+                    const float a0 = pli[0][r * RS], a1 = pli[2][r * RS];
+                    o[0] = fmaf(sg[0], a0, cst[0]) - plj[0][r * RS];
+                    o[1] = fmaf(-chain_m[0], a0, pli[1][r * RS]);
+                    o[2] = fmaf(sg[2], a1, cst[2]) - plj[2][r * RS];
+                    o[3] = fmaf(-chain_m[1], a1, pli[3][r * RS]);
+                } else {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) o[k] = fmaf(sg[k], pli[k][r * RS], cst[k]) - plj[k][r * RS];
+                    for (int k = 0; k < 4; ++k) o[k] = fmaf(sg[k], pli[k][r * RS], cst[k]) - plj[k][r * RS];
+                }
                 // every occupancy must be a number >= 0 up to rounding: catches overflow / NaN anywhere upstream
                 if (!(fminf(o[0], o[1]) >= lim0)) bad_occ |= 1;
                 if (!(fminf(o[2], o[3]) >= lim1)) bad_occ |= 2;
@@ -748,14 +800,17 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 w1 += gstride;
             }
         }
+        PT(7)                                           // bwd: gradient rows
     };
 
     if (nch >= 2) load_chunk(nch - 2);
+    load_ckpt(nch - 1);
     for (int j = nch - 1; j >= 0; --j) {
         int t0;
         if (chunk_geom(j, t0)) bwd_chunk(IC<KF>{}, j, t0);
         else bwd_chunk(IC<1>{}, j, t0);
     }
+    PT_FLUSH
     {   // beta must have stayed finite to the very first frame (a blank state's overflow shows nowhere else)
 #pragma unroll
         for (int jj = 0; jj < NSL; ++jj) {
@@ -839,6 +894,17 @@ int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
 }
 
 }  // namespace
+
+#ifdef MDD_PAIR_TIMING
+extern "C" void mdd_debug_phase_cycles(unsigned long long* out, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_phase_cycles, sizeof(unsigned long long) * 16);
+    if (reset) {
+        unsigned long long z[16] = {0};
+        cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z));
+    }
+}
+#endif
 
 bool ctc_pair_supported(int C, int Lmax) { return C <= 63 && pick_nsl(Lmax) != 0; }   // C classes + the zero item <= 64 slots
 
