@@ -291,9 +291,6 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             const int i = lane * NL + q;
             atomicOr(&gm[h * 72 + (i < L[h] ? lab[h * 256 + i] : C)], 1 << q);
         }
-        // the row commit / read-back accesses: all first columns of the lanes together, all second columns together
-        if (cols.v0) atomicOr(&gm[h * 72 + cols.c0], 1 << NL);
-        if (cols.v1) atomicOr(&gm[h * 72 + cols.c1], 1 << (NL + 1));
     }
     __syncwarp();
 #pragma unroll
