@@ -24,6 +24,13 @@ extern "C" int64_t mdd_launch_count(void) { return g_launch_count; }
 extern "C" void mdd_launch_count_reset(void) { g_launch_count = 0; }
 
 namespace {
+// which linear-domain kernel serves this shape: the pair kernel where it applies, else the scalar one (C = 64)
+int ctc_kernel_choice(int C, int Lmax, int algo) {
+    if (algo == 1) return 0;
+    if (algo != 3 && ctc_pair_supported(C, Lmax)) return 1;
+    if (algo != 2 && ctc_fast_supported(C, Lmax)) return 2;
+    return 0;
+}
 struct CtcWs {
     size_t off_offsets, off_flags, off_ckpt, off_fast, total;
 };
@@ -33,10 +40,11 @@ CtcWs ctc_ws_layout(int T, int B, int C, int Lmax, int algo) {
     w.off_offsets = o; o = align_up(o + (size_t)B * 8, 256);
     w.off_flags = o;   o = align_up(o + (size_t)B * 4, 256);
     w.off_ckpt = o;
-    const bool fast = algo != 1 && ctc_fast_supported(C, Lmax) && ctc_pair_supported(C, Lmax);
-    if (algo == 1 || !fast || algo == 0 || algo == 3) o = align_up(o + ctc_log_ckpt_bytes(T, B, Lmax), 256);
+    const int kern = ctc_kernel_choice(C, Lmax, algo);           // 0 log-space only, 1 pair kernel, 2 scalar kernel
+    if (algo != 2) o = align_up(o + ctc_log_ckpt_bytes(T, B, Lmax), 256);
     w.off_fast = o;
-    if (fast) o = align_up(o + (algo == 3 ? ctc_fast_ws_bytes(T, B, Lmax) : ctc_pair_ws_bytes(T, B, Lmax)), 256);
+    if (kern == 1) o = align_up(o + ctc_pair_ws_bytes(T, B, Lmax), 256);
+    if (kern == 2) o = align_up(o + ctc_fast_ws_bytes(T, B, Lmax), 256);
     w.total = o;
     return w;
 }
@@ -79,11 +87,11 @@ extern "C" int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t
         rc = launch_tgt_offsets(target_lengths, B, reinterpret_cast<int64_t*>(ws + w.off_offsets), st);
         if (rc) return rc;
     }
-    const bool fast = algo != 1 && ctc_fast_supported(C, max_target_len) && ctc_pair_supported(C, max_target_len) && T > 0;
-    if (algo == 2 && !fast) return MDD_E_UNSUPPORTED;
-    if (fast) {
+    const int kern = T > 0 ? ctc_kernel_choice(C, max_target_len, algo) : 0;
+    if (algo == 2 && kern != 1) return MDD_E_UNSUPPORTED;
+    if (kern) {
         // flags[b] != 0 on return -> utterance needs the log-space path
-        rc = algo == 3 ? launch_ctc_fast(p, ws + w.off_fast, st) : launch_ctc_pair(p, ws + w.off_fast, st);
+        rc = kern == 2 ? launch_ctc_fast(p, ws + w.off_fast, st) : launch_ctc_pair(p, ws + w.off_fast, st);
         if (rc) return rc;
         if (algo == 0 || algo == 3) {
             p.only_flagged = 1;

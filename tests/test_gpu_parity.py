@@ -120,7 +120,7 @@ def test_ctc_other_class_counts(M, C):
     il = torch.randint(60, T + 1, (B,), generator=g)
     tl = torch.randint(0, L + 1, (B,), generator=g)
     for algo in (1, 0):
-        _check_ctc(M, lp, tg, il, tl, algo=algo, max_fallback=0 if C < 64 else None)
+        _check_ctc(M, lp, tg, il, tl, algo=algo, max_fallback=0)
 
 
 def test_ctc_peaky_and_extreme_inputs(M):
