@@ -85,27 +85,6 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
 }
 __device__ __forceinline__ float compc(const float2& v, int h) { return h ? v.y : v.x; }
 
-// Two floats per lane per utterance row.  VEC: columns (2*lane, 2*lane+1) as one 8-byte access, else (lane, lane+32).
-struct Cols {
-    int c0, c1;
-    bool v0, v1;
-    int l0, l1;
-};
-template <bool VEC>
-__device__ __forceinline__ Cols make_cols(int lane, int C) {
-    Cols k;
-    if constexpr (VEC) { k.c0 = 2 * lane; k.c1 = 2 * lane + 1; k.v0 = k.v1 = (2 * lane < C); }
-    else { k.c0 = lane; k.c1 = lane + 32; k.v0 = lane < C; k.v1 = lane + 32 < C; }
-    k.l0 = k.v0 ? k.c0 : 0;
-    k.l1 = k.v1 ? k.c1 : 0;
-    return k;
-}
-template <bool VEC>
-__device__ __forceinline__ void st_row2_gmem(float* __restrict__ dst, const Cols& k, float2 v) {
-    if constexpr (VEC) { if (k.v0) __stcs(reinterpret_cast<float2*>(dst + k.c0), v); }
-    else { if (k.v0) __stcs(dst + k.c0, v.x); if (k.v1) __stcs(dst + k.c1, v.y); }
-}
-
 // ---------------------------------------------------------------------------------------------------------------
 // One lattice step for both utterances.  Lane l owns states s = NSL*l + j; even j = blank, odd j = label (j-1)/2.
 //   alpha: new[s] = (a[s] + a[s-1] + ma * a[s-2]) * e[s]
@@ -212,7 +191,7 @@ __host__ __device__ inline PairSmem pair_smem_layout(int NSL, int RS, bool regbu
     return s;
 }
 
-template <int NSL, bool VEC, bool REGBUF, int MAXR>
+template <int NSL, bool REGBUF, int MAXR>
 __global__ void __maxnreg__(MAXR)
 ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     using G = PGeo<NSL>;
@@ -239,7 +218,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     int* lab = scratch;
     int* slot = scratch + 512;
     int* ctab = scratch + 1024;
-    static_assert(KF * (G::RS + RW) >= 1280 + 288, "setup scratch must fit in the product + emission rows");
+    static_assert(KF * (G::RS + RW) >= 1280 + 288 + 128, "setup scratch must fit in the product + emission rows");
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const int b = 2 * pair + h;
@@ -271,8 +250,6 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     }
     if (!act[0] && !act[1]) return;
     __syncwarp();
-
-    const Cols cols = make_cols<VEC>(lane, C);
 
     // Emission layout.  The lattice gathers e[t][label] with one LDS per label state; with C > 32 classes a plain row
     // makes two of the requested classes share a bank in almost every gather.  Per utterance, classes (and the zero
@@ -331,6 +308,26 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             if (valid[k]) cpos[h * 72 + lane + 32 * k] = posk[k];
     }
     __syncwarp();
+    // Row ownership follows the layout: lane l commits (and later differentiates) the class placed in bank l of each
+    // level, so that the row commit, its read-back and the staged row itself are conflict-free by construction.
+    int* ipos = scratch + 1280 + 288;                            // [2][64] class at a position, -1 = none / zero slot
+    for (int i = lane; i < 128; i += 32) ipos[i] = -1;
+    __syncwarp();
+    for (int c = lane; c < C; c += 32) {
+        ipos[cpos[c]] = c;
+        ipos[64 + cpos[72 + c]] = c;
+    }
+    __syncwarp();
+    int oc[2][2];                                                // my class of utterance h at level k (clamped to 0)
+    bool ov[2][2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int c = ipos[h * 64 + k * 32 + lane];
+            ov[h][k] = c >= 0;
+            oc[h][k] = c >= 0 ? c : 0;
+        }
 
     // per-lane constants: emission pointers and skip masks of my label states
     const float* ep0[NL];
@@ -356,9 +353,6 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     }
     const float* bl0 = rows + cpos[blank];
     const float* bl1 = rows + CPMAX + cpos[72 + blank];
-    // where my two columns of a log-prob row live in the staged row (w[2h+k]) and where the zero slots are
-    int wr[4];
-    wr[0] = cpos[cols.l0]; wr[1] = cpos[cols.l1]; wr[2] = CPMAX + cpos[72 + cols.l0]; wr[3] = CPMAX + cpos[72 + cols.l1];
     const int zslot0 = cpos[C], zslot1 = CPMAX + cpos[72 + C];
 
     // class-sorted slots.  Label i of utterance h gets slot perm(i) of a list sorted by class (positions ascending
@@ -369,8 +363,6 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     const float* plj[4];
     float sg[4];
     bool isblank[4];
-    float chain_m[2] = {0.f, 0.f};
-    const bool chain = VEC && blank == 0;                        // P[pe(c1)] is P[E(c0)] or 0: three lookups, not four
     int st_split[2], st_pad[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -428,8 +420,8 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         }
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
-            const int c = k ? cols.c1 : cols.c0;
-            const bool valid = k ? cols.v1 : cols.v0;
+            const int c = oc[h][k];
+            const bool valid = ov[h][k];
             int oi = ZERO, oj = ZERO;
             float sgn = 1.f;
             bool isb = false;
@@ -446,7 +438,6 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 if (st + n > 0) oi = slotpos(st + n - 1);
                 if (n == 0) oj = oi;
                 else if (!(st == 0 || st == split)) oj = slotpos(st - 1);
-                if (k == 1) chain_m[h] = (oj == ZERO) ? 0.f : 1.f;    // second column continues the first one's prefix
             }
             pli[2 * h + k] = prod + oi;
             plj[2 * h + k] = prod + oj;
@@ -479,9 +470,12 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     };
     // rows are always read from a live utterance's memory; an idle half re-reads its partner's rows
     const int bsrc0 = act[0] ? bidx[0] : bidx[1], bsrc1 = act[1] ? bidx[1] : bidx[0];
-    const float* lp0 = p.lp + (size_t)bsrc0 * p.stride_b + cols.l0;
-    const float* lp1 = p.lp + (size_t)bsrc1 * p.stride_b + cols.l0;
-    const int dl1 = cols.l1 - cols.l0;
+    const float* lpb0 = p.lp + (size_t)bsrc0 * p.stride_b;
+    const float* lpb1 = p.lp + (size_t)bsrc1 * p.stride_b;
+    const float* lp00 = lpb0 + oc[0][0];                         // my level-0 / level-1 class of each utterance
+    const float* lp01 = lpb0 + oc[0][1];
+    const float* lp10 = lpb1 + oc[1][0];
+    const float* lp11 = lpb1 + oc[1][1];
     const size_t gstride = (size_t)p.B * C;
     float* gr0 = want_grad ? p.grad + (size_t)bidx[0] * C : nullptr;
     float* gr1 = want_grad ? p.grad + (size_t)bidx[1] * C : nullptr;
@@ -490,21 +484,14 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     for (int h = 0; h < 2; ++h) g[h] = act[h] ? (p.grad_out ? p.grad_out[bidx[h]] : 1.f) * p.gscalar : 0.f;
 
     float2 pre0[KF], pre1[KF];                          // the next chunk's rows, in flight
-    auto load_rows = [&](auto nfc, int t0) {
+    auto load_rows = [&](auto nfc, int t0) {             // pre0[r] = (level 0, level 1) of the first utterance, ...
         constexpr int NF = decltype(nfc)::value;
-        const float* s0 = lp0 + (size_t)t0 * p.stride_t;
-        const float* s1 = lp1 + (size_t)t0 * p.stride_t;
+        size_t o = (size_t)t0 * p.stride_t;
 #pragma unroll
         for (int r = 0; r < NF; ++r) {
-            if constexpr (VEC) {
-                pre0[r] = __ldcs(reinterpret_cast<const float2*>(s0));
-                pre1[r] = __ldcs(reinterpret_cast<const float2*>(s1));
-            } else {
-                pre0[r] = make_float2(__ldcs(s0), __ldcs(s0 + dl1));
-                pre1[r] = make_float2(__ldcs(s1), __ldcs(s1 + dl1));
-            }
-            s0 += p.stride_t;
-            s1 += p.stride_t;
+            pre0[r] = make_float2(__ldcs(lp00 + o), __ldcs(lp01 + o));
+            pre1[r] = make_float2(__ldcs(lp10 + o), __ldcs(lp11 + o));
+            o += p.stride_t;
         }
     };
     auto load_chunk = [&](int j) {
@@ -514,8 +501,10 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     };
     auto put_row = [&](int r, float2 v0, float2 v1) {
         float* d = rows + r * RW;
-        if (cols.v0) { d[wr[0]] = v0.x; d[wr[2]] = v1.x; }
-        if (cols.v1) { d[wr[1]] = v0.y; d[wr[3]] = v1.y; }
+        if (ov[0][0]) d[lane] = v0.x;
+        if (ov[0][1]) d[32 + lane] = v0.y;
+        if (ov[1][0]) d[CPMAX + lane] = v1.x;
+        if (ov[1][1]) d[CPMAX + 32 + lane] = v1.y;
     };
     auto commit_rows = [&](auto nfc, bool kill0, bool kill1) {   // p = exp(lp) into shared memory; an idle half emits zeros
         constexpr int NF = decltype(nfc)::value;
@@ -554,8 +543,12 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     load_chunk(0);
     if (want_grad) {                                    // rows t >= T_max of the gradient are zero (torch semantics)
         for (int t = Tmax; t < T; ++t) {
-            if (act[0]) st_row2_gmem<VEC>(gr0 + (size_t)t * gstride, cols, make_float2(0.f, 0.f));
-            if (act[1]) st_row2_gmem<VEC>(gr1 + (size_t)t * gstride, cols, make_float2(0.f, 0.f));
+            float* z0 = gr0 + (size_t)t * gstride;
+            float* z1 = gr1 + (size_t)t * gstride;
+            if (act[0] && ov[0][0]) __stcs(z0 + oc[0][0], 0.f);
+            if (act[0] && ov[0][1]) __stcs(z0 + oc[0][1], 0.f);
+            if (act[1] && ov[1][0]) __stcs(z1 + oc[1][0], 0.f);
+            if (act[1] && ov[1][1]) __stcs(z1 + oc[1][1], 0.f);
         }
     }
 
@@ -579,7 +572,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 const int r = idx / 6, u = (idx % 6) / 3, part = idx % 3;
                 const int t = t0 + 2 * KF + r;
                 if (idx < 6 * KF && t < Tmax) {
-                    const float* q = (u ? lp1 : lp0) - cols.l0 + (size_t)t * p.stride_t + min(part * 32, C - 1);
+                    const float* q = (u ? lpb1 : lpb0) + (size_t)t * p.stride_t + min(part * 32, C - 1);
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
                 }
             }
@@ -769,32 +762,26 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             const float g0 = kill0 ? 0.f : g[0], g1 = kill1 ? 0.f : g[1];
             const float zg0 = zi[0] * g0, zg1 = zi[1] * g1;
             const float lim0 = kill0 ? -3.0e38f : -1e-3f * zc[0], lim1 = kill1 ? -3.0e38f : -1e-3f * zc[1];
-            float* w0 = gr0 + (size_t)t0 * gstride;
-            float* w1 = gr1 + (size_t)t0 * gstride;
+            const bool s00 = act[0] && ov[0][0], s01 = act[0] && ov[0][1], s10 = act[1] && ov[1][0], s11 = act[1] && ov[1][1];
+            float* w00 = gr0 + (size_t)t0 * gstride + oc[0][0];
+            float* w01 = gr0 + (size_t)t0 * gstride + oc[0][1];
+            float* w10 = gr1 + (size_t)t0 * gstride + oc[1][0];
+            float* w11 = gr1 + (size_t)t0 * gstride + oc[1][1];
 #pragma unroll
             for (int r = 0; r < NF; ++r) {
                 const float* d = rows + r * RW;
-                const float2 pv0 = make_float2(d[wr[0]], d[wr[1]]), pv1 = make_float2(d[wr[2]], d[wr[3]]);
+                const float2 pv0 = make_float2(d[lane], d[32 + lane]), pv1 = make_float2(d[CPMAX + lane], d[CPMAX + 32 + lane]);
                 float o[4];
-                if (chain) {
-                    const float a0 = pli[0][r * RS], a1 = pli[2][r * RS];
-                    o[0] = fmaf(sg[0], a0, cst[0]) - plj[0][r * RS];
-                    o[1] = fmaf(-chain_m[0], a0, pli[1][r * RS]);
-                    o[2] = fmaf(sg[2], a1, cst[2]) - plj[2][r * RS];
-                    o[3] = fmaf(-chain_m[1], a1, pli[3][r * RS]);
-                } else {
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) o[k] = fmaf(sg[k], pli[k][r * RS], cst[k]) - plj[k][r * RS];
-                }
+                for (int k = 0; k < 4; ++k) o[k] = fmaf(sg[k], pli[k][r * RS], cst[k]) - plj[k][r * RS];
                 // every occupancy must be a number >= 0 up to rounding: catches overflow / NaN anywhere upstream
                 if (!(fminf(o[0], o[1]) >= lim0)) bad_occ |= 1;
                 if (!(fminf(o[2], o[3]) >= lim1)) bad_occ |= 2;
-                if (act[0])
-                    st_row2_gmem<VEC>(w0, cols, make_float2(fmaf(-o[0], zg0, pv0.x * g0), fmaf(-o[1], zg0, pv0.y * g0)));
-                if (act[1])
-                    st_row2_gmem<VEC>(w1, cols, make_float2(fmaf(-o[2], zg1, pv1.x * g1), fmaf(-o[3], zg1, pv1.y * g1)));
-                w0 += gstride;
-                w1 += gstride;
+                if (s00) __stcs(w00, fmaf(-o[0], zg0, pv0.x * g0));
+                if (s01) __stcs(w01, fmaf(-o[1], zg0, pv0.y * g0));
+                if (s10) __stcs(w10, fmaf(-o[2], zg1, pv1.x * g1));
+                if (s11) __stcs(w11, fmaf(-o[3], zg1, pv1.y * g1));
+                w00 += gstride; w01 += gstride; w10 += gstride; w11 += gstride;
             }
         }
         PT(7)                                           // bwd: gradient rows
@@ -836,7 +823,7 @@ int env_int(const char* name, int dflt) {
     return e ? atoi(e) : dflt;
 }
 
-template <int NSL, bool VEC, bool REGBUF, int MAXR>
+template <int NSL, bool REGBUF, int MAXR>
 int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
     const PairSmem lay = pair_smem_layout(NSL, PGeo<NSL>::RS, REGBUF);
     size_t smem = (size_t)lay.total_floats * 4;                  // one warp (= one pair) per CTA
@@ -847,7 +834,7 @@ int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
     int wps = wps_env;
     if (wps <= 0) {
         double best = 0.0;
-        const int wmax = MAXR >= 255 ? 8 : MAXR >= 168 ? 12 : MAXR >= 144 ? 14 : 16;
+        const int wmax = MAXR >= 255 ? 8 : 12;
         for (int w = wmax; w >= wmax - 2; --w) {
             const long long slots = (long long)kNumSM * w;
             const double eff = (double)npairs / (double)(((npairs + slots - 1) / slots) * slots);
@@ -860,7 +847,7 @@ int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
     }
     static size_t configured = 0;
     if (configured < smem) {
-        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, VEC, REGBUF, MAXR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, REGBUF, MAXR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem) != cudaSuccess) {
             cudaGetLastError();
             return MDD_E_CUDA;
@@ -868,26 +855,21 @@ int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
         configured = smem;
     }
     const int n_ckpt = p.T / KF + 2 * KF;
-    ctc_pair_kernel<NSL, VEC, REGBUF, MAXR><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
+    ctc_pair_kernel<NSL, REGBUF, MAXR><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
     MDD_CHECK_LAUNCH();
     return MDD_OK;
 }
 
 template <int NSL>
 int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
-    const bool vec = (p.C % 2 == 0) && (p.stride_t % 2 == 0) && (p.stride_b % 2 == 0) && ((uintptr_t)p.lp % 8 == 0) &&
-                     (!p.grad || (uintptr_t)p.grad % 8 == 0);
     if constexpr (NSL == 8) {
         static int regbuf = env_int("MDD_CTC_PAIR_REGBUF", 1), maxr = env_int("MDD_CTC_PAIR_MAXR", 255);
-        if (vec) {
-            if (regbuf) return launch_cfg<NSL, true, true, 255>(p, ws, st);
-            if (maxr >= 255) return launch_cfg<NSL, true, false, 255>(p, ws, st);
-            if (maxr >= 168) return launch_cfg<NSL, true, false, 168>(p, ws, st);
-            if (maxr >= 144) return launch_cfg<NSL, true, false, 144>(p, ws, st);
-            return launch_cfg<NSL, true, false, 128>(p, ws, st);
-        }
+        if (regbuf) return launch_cfg<NSL, true, 255>(p, ws, st);
+        if (maxr >= 255) return launch_cfg<NSL, false, 255>(p, ws, st);
+        return launch_cfg<NSL, false, 168>(p, ws, st);
     }
-    return vec ? launch_cfg<NSL, true, false, 168>(p, ws, st) : launch_cfg<NSL, false, false, 168>(p, ws, st);
+    if constexpr (NSL < 8) return launch_cfg<NSL, true, 255>(p, ws, st);
+    return launch_cfg<NSL, false, 255>(p, ws, st);               // NSL = 16: the alpha buffer does not fit in registers
 }
 
 }  // namespace
