@@ -489,8 +489,12 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         size_t o = (size_t)t0 * p.stride_t;
 #pragma unroll
         for (int r = 0; r < NF; ++r) {
-            pre0[r] = make_float2(__ldcs(lp00 + o), __ldcs(lp01 + o));
-            pre1[r] = make_float2(__ldcs(lp10 + o), __ldcs(lp11 + o));
+            // volatile: these stay where they are written.  A warp waits on a scoreboard for ALL loads counted on
+            // it, so row loads issued ahead of a consumer of the checkpoint would put their DRAM latency in its way.
+            asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre0[r].x) : "l"(lp00 + o));
+            asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre0[r].y) : "l"(lp01 + o));
+            asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre1[r].x) : "l"(lp10 + o));
+            asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre1[r].y) : "l"(lp11 + o));
             o += p.stride_t;
         }
     };
@@ -557,7 +561,9 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
 #ifdef MDD_PAIR_TIMING
         PT(2)
-        asm volatile("" ::"f"(pre0[0].x), "f"(pre1[NF - 1].y));
+        { float d2, d3;
+          asm volatile("mov.f32 %0, %2; mov.f32 %1, %3;" : "=f"(d2), "=f"(d3) : "f"(pre0[0].x), "f"(pre1[NF - 1].y));
+          if (d2 == 1.2345f && d3 == d2) flag[0] |= 1 << 30; }
         PT(11)                                          // fwd: waiting for the rows
 #endif
         __syncwarp();
@@ -669,11 +675,13 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             __syncwarp();
             commit_rows(nfc, kill0, kill1);
             __syncwarp();
-            if (j > 0) load_chunk(j - 1);
         }
         PT(9)                                           // bwd: commit + row loads
 #ifdef MDD_PAIR_TIMING
-        asm volatile("" ::"r"(ea[0]), "r"(ea[1]), "f"(a[0].x), "f"(a[NSL - 1].y));
+        { int d0, d1; float d2, d3;                       // real consumers: wait for the checkpoint to land
+          asm volatile("mov.b32 %0, %4; mov.b32 %1, %5; mov.f32 %2, %6; mov.f32 %3, %7;"
+                       : "=r"(d0), "=r"(d1), "=f"(d2), "=f"(d3) : "r"(ea[0]), "r"(ea[1]), "f"(a[0].x), "f"(a[NSL - 1].y));
+          if (d0 == 0x7fffffff && d1 == d0 && d2 == 1.2345f && d3 == d2) flag[0] |= 1 << 30; }
         PT(10)                                          // bwd: waiting for the checkpoint
 #endif
         // a / ea hold the checkpoint of this chunk: boundary factors and the beta exponents that go with it
@@ -707,7 +715,8 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 if (s == S[1] - 1) bt[jj].y += ini[1];
             }
         }
-        PT(3)                                           // bwd: commit, prefetch, exponent bookkeeping
+        if (j < nch - 1 && j > 0) load_chunk(j - 1);    // after the checkpoint's consumers (see load_rows)
+        PT(3)                                           // bwd: commit, exponent bookkeeping, row loads
         // recompute alpha over the chunk, keeping the label states
         float2 A[REGBUF ? NF : 1][NL];
 #pragma unroll

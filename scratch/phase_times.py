@@ -3,7 +3,8 @@ sys.path.insert(0, '.')
 import mddctc
 from mddctc.loss import ctc_loss_raw
 L = mddctc._lib.lib()
-T,B,C,Lb = 1000,4096,42,120
+import os
+T,B,C,Lb = 1000,int(os.environ.get("PT_B","4096")),42,120
 g = torch.Generator().manual_seed(1)
 lp = torch.log_softmax(torch.randn(T,B,C,generator=g),-1).cuda()
 tg = torch.randint(1,C,(B,Lb),generator=g).cuda()
