@@ -671,6 +671,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     auto bwd_chunk = [&](auto nfc, int j, int t0) {
         constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
+        load_ckpt(j);                                   // from L2; lands while the rows are exponentiated
         if (j < nch - 1) {                              // the last chunk is still staged (and exponentiated)
             __syncwarp();
             commit_rows(nfc, kill0, kill1);
@@ -748,7 +749,12 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 pp1[q][r * RS] = pl.y;
             }
         }
-        if (j > 0) load_ckpt(j - 1);                    // the alpha buffer is dead: the next checkpoint travels meanwhile
+        if (j > 0) {                                    // pull the next chunk's checkpoint into L2 meanwhile (no register
+            const float* c = ck + (size_t)(j - 1) * CKW;    // destination, hence no scoreboard shared with the LDS traffic)
+#pragma unroll
+            for (int q = 0; q < NSL / 2; ++q) asm volatile("prefetch.global.L2 [%0];" ::"l"(c + (q * 32 + lane) * 4));
+            if (lane < 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(c + 64 * NSL + lane * 32));
+        }
         __syncwarp();
         PT(5)                                           // bwd: beta + product scatter
         // in-place prefix sums of the sorted products: lane = (frame, utterance, stretch)
@@ -797,7 +803,6 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     };
 
     if (nch >= 2) load_chunk(nch - 2);
-    load_ckpt(nch - 1);
     for (int j = nch - 1; j >= 0; --j) {
         int t0;
         if (chunk_geom(j, t0)) bwd_chunk(IC<KF>{}, j, t0);
