@@ -14,7 +14,7 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-SO_PATH = os.path.join(_HERE, "libmddctc.so")
+SO_PATH = os.environ.get("MDD_SO_PATH") or os.path.join(_HERE, "libmddctc.so")   # override: experiment builds only
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",

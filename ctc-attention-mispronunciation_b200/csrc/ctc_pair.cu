@@ -71,7 +71,7 @@ struct PGeo {
 };
 
 __device__ __forceinline__ float pow2i(int x) {            // 2^x, 0 below the normal range, clamped at 2^127
-    return x < -126 ? 0.f : __int_as_float((127 + min(x, 127)) << 23);
+    return __int_as_float((min(max(x, -127), 127) + 127) << 23);   // branch-free: exponent field 0 is +0.0
 }
 __device__ __forceinline__ float fast_exp(float x) {
     float y;
