@@ -18,7 +18,7 @@ keys = ['dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__dram_throughput.a
         'lts__t_sector_hit_rate.pct', 'sm__throughput.avg.pct_of_peak_sustained_elapsed']
 keys += sorted(k for k in d if k.startswith('smsp__average_warps_issue_stalled') and k.endswith('per_issue_active.ratio'))
 out = ["# ncu --set full --clock-control none --import-source on -k regex:ctc_pair -s 3 -c 1 python bench.py --steps 2 --warmup 3 --no-cpu",
-       "# kernel: ctc_pair_kernel<NSL=8,VEC,REGBUF,255> (two utterances per warp, packed FP32), BASELINE config 3 (T=1000,B=4096,C=42,L=120), one launch",
+       "# kernel: ctc_pair_kernel<NSL=8,REGBUF,255> (two utterances per warp, packed FP32), BASELINE config 3 (T=1000,B=4096,C=42,L=120), one launch",
        "# algorithmic bytes per launch 1.376e9 (4*C*sum(T_b) read + 4*C*T*B written); 4.096e6 utterance-frames"]
 for k in keys:
     if k in d:
@@ -30,7 +30,7 @@ open('profiles/r1_ncu_full_ctc_pair.txt', 'w').write("\n".join(out) + "\n")
 r, w = float(d['dram__bytes_read.sum'][1]), float(d['dram__bytes_write.sum'][1])
 assert d['dram__bytes_read.sum'][0] == 'Gbyte' and d['dram__bytes_write.sum'][0] == 'Gbyte'
 t = json.load(open('profiles/ncu_traffic.json'))
-e = {"bytes": int((r + w) * 1e9), "kernel": "ctc_pair_kernel<8,true,true,255>", "dram__bytes_read.sum": int(r * 1e9),
+e = {"bytes": int((r + w) * 1e9), "kernel": "ctc_pair_kernel<8,true,255>", "dram__bytes_read.sum": int(r * 1e9),
      "dram__bytes_write.sum": int(w * 1e9), "source": "profiles/r1_ncu_full_ctc_pair.txt (ncu --set full, one launch, BASELINE config 3)"}
 t['c3/algo0'] = e
 t['c3/algo2'] = e
