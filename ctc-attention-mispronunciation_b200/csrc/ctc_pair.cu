@@ -60,10 +60,7 @@ template <int NSL>
 struct PGeo {
     static constexpr int NL = NSL / 2;                     // label states per lane
     static constexpr int LCAP = 16 * NSL - 1;              // S = 2L+1 <= 32*NSL - 1
-    static constexpr int U1OFF = ((LCAP + 3 + 3) & ~3) + 4;    // second utterance's sorted list inside a product row
-    static constexpr int RS = ((U1OFF + LCAP + 3 + 2 - 4 + 31) / 32) * 32 + 4;   // product row stride, == 4 (mod 32)
-    static constexpr int ZERO = RS - 1;                    // always 0 (past the sorted lists and the alpha row)
-    static constexpr int DUMP = RS - 2;                    // swallows products of unused label slots
+    static constexpr int ARS = 32 * NSL;                   // (!REGBUF) floats per frame of the alpha label-state buffer
     // mass can cross ceil(2*KF/NSL)+1 lane boundaries between two renormalisations, each multiplying the mantissa by
     // up to 2^GAP, plus 3^KF of growth: GAP * crossings + 14 < 126
     static constexpr int GAP = NSL == 2 ? 12 : NSL == 4 ? 22 : NSL == 8 ? 36 : 56;
@@ -179,14 +176,14 @@ __device__ __forceinline__ void renorm_alpha(float2 (&a)[NSL], int (&ea)[2], flo
 }
 
 struct PairSmem {
-    int prod_off, rows_off, abuf_off, total_floats;
+    int occ_off, rows_off, abuf_off, total_floats;
 };
-__host__ __device__ inline PairSmem pair_smem_layout(int NSL, int RS, bool regbuf) {
+__host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf) {
     PairSmem s;
     int o = 0;
-    s.prod_off = o; o += KF * RS;                 // class-sorted label products -> prefix sums (setup scratch too)
+    s.occ_off = o; o += KF * RW;                  // class occupancies of the chunk, fixed point (setup scratch too)
     s.rows_off = o; o += KF * RW;                 // exp(lp) rows of the current chunk, both utterances
-    s.abuf_off = 0;                               // (!regbuf) alpha label states of frame r live in product row r
+    s.abuf_off = o; if (!regbuf) o += KF * 32 * NSL;   // alpha label states of the chunk when they do not fit in registers
     s.total_floats = (o + 3) & ~3;
     return s;
 }
@@ -195,18 +192,19 @@ template <int NSL, bool REGBUF, int MAXR>
 __global__ void __maxnreg__(MAXR)
 ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     using G = PGeo<NSL>;
-    constexpr int NL = G::NL, RS = G::RS, U1OFF = G::U1OFF, ZERO = G::ZERO, DUMP = G::DUMP, CKW = G::CKW;
+    constexpr int NL = G::NL, ARS = G::ARS, CKW = G::CKW;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int pair = blockIdx.x * (blockDim.x >> 5) + warp;
     const int npairs = (p.B + 1) >> 1;
     if (pair >= npairs) return;
 
     extern __shared__ __align__(16) float smem_f[];
-    const PairSmem lay = pair_smem_layout(NSL, RS, REGBUF);
+    const PairSmem lay = pair_smem_layout(NSL, REGBUF);
     float* base = smem_f + (size_t)warp * lay.total_floats;
-    float* prod = base + lay.prod_off;                           // [KF][RS]
+    unsigned* occ = reinterpret_cast<unsigned*>(base + lay.occ_off);   // [KF][RW], laid out like the emission rows
     float* rows = base + lay.rows_off;                           // [KF][RW]
-    static_assert(REGBUF || PGeo<NSL>::RS >= 32 * NSL, "alpha label row must fit in a product row");
+    float* abuf = base + lay.abuf_off;                           // [KF][ARS] (!REGBUF)
+    constexpr int OCCD = -KF * RW;                               // occupancy cell of an emission slot: rows -> occ
 
     const int C = p.C, blank = p.blank, T = p.T;
     const bool want_grad = p.grad != nullptr;
@@ -214,11 +212,10 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     // ------------------------------------------------------------------------------------------ per-utterance setup
     int bidx[2], Tb[2], L[2], S[2];
     bool act[2];
-    int* scratch = reinterpret_cast<int*>(prod);                 // lab[2][256] | slot[2][256] | ctab[2][128]
+    int* scratch = reinterpret_cast<int*>(occ);                  // lab[2][256] | hist[2][64] | ...
     int* lab = scratch;
-    int* slot = scratch + 512;
-    int* ctab = scratch + 1024;
-    static_assert(KF * (G::RS + RW) >= 1280 + 288 + 128, "setup scratch must fit in the product + emission rows");
+    int* hist = scratch + 512;
+    static_assert(2 * KF * RW >= 1280 + 288 + 128, "setup scratch must fit in the occupancy + emission rows");
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const int b = 2 * pair + h;
@@ -355,102 +352,36 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     const float* bl1 = rows + CPMAX + cpos[72 + blank];
     const int zslot0 = cpos[C], zslot1 = CPMAX + cpos[72 + C];
 
-    // class-sorted slots.  Label i of utterance h gets slot perm(i) of a list sorted by class (positions ascending
-    // inside a class), cut at the class boundary nearest L/2 into two stretches; the second starts 16-byte aligned.
-    float* pp0[NL];                                              // product slot of my label states (frame 0)
-    float* pp1[NL];
-    const float* pli[4];                                         // occupancy = sg * P[li] + cst - P[lj]
-    const float* plj[4];
-    float sg[4];
-    bool isblank[4];
-    int st_split[2], st_pad[2];
+    // Class reduction.  occupancy_c(t) = sum of alpha*u over the label states of class c is accumulated with
+    // shared-memory integer atomics: a product, scaled to a fraction of Z (<= 1) times 2^23 * 0.999, is rounded to an
+    // integer by adding 2^23 in fp32, and the BIT PATTERN is added to the class cell (the n_c copies of the bias
+    // 0x4B000000 are subtracted by the reader).  Integer addition is associative, so the result does not depend on the
+    // order in which conflicting lanes are served: bitwise reproducible.  The cell of a class sits at the same
+    // position as its emission (bank-coloured), so the emission pointers address it and the owner lane reads it back
+    // without conflicts.  Resolution 1.2e-7 of Z per product.
+    unsigned nbias[4];                                           // n_c * bias of my classes: [2*h + level]
+    for (int i = lane; i < 128; i += 32) hist[i] = 0;
+    __syncwarp();
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        const int Lh = L[h];
-        int cnt[2] = {0, 0};
-        for (int i = 0; i < Lh; ++i) {
-            const int v = lab[h * 256 + i];
-            cnt[0] += (v == lane);
-            cnt[1] += (v == lane + 32);
-        }
-        int start[2], basek = 0;
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            int inc = cnt[k];
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int o = __shfl_up_sync(FULL, inc, d);
-                if (lane >= d) inc += o;
-            }
-            start[k] = basek + inc - cnt[k];
-            basek += __shfl_sync(FULL, inc, 31);
-        }
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const int c = lane + 32 * k;
-            ctab[h * 128 + c] = start[k];
-            ctab[h * 128 + 64 + c] = cnt[k];
-            if (cnt[k] > 0) {
-                int w = start[k];
-                for (int i = 0; i < Lh; ++i)
-                    if (lab[h * 256 + i] == c) slot[h * 256 + i] = w++;
-            }
-        }
-        int best = 0x7fffffff;
-        const int want = Lh >> 1;
-#pragma unroll
-        for (int k = 0; k < 2; ++k)
-            if (cnt[k] > 0) best = min(best, abs(start[k] - want) * 1024 + start[k]);
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(FULL, best, d));
-        const int split = (best == 0x7fffffff) ? 0 : (best & 1023);
-        const int pad = ((split + 3) & ~3) - split;
-        st_split[h] = split;
-        st_pad[h] = pad;
-        __syncwarp();
+    for (int h = 0; h < 2; ++h)
 #pragma unroll
         for (int q = 0; q < NL; ++q) {
             const int i = lane * NL + q;
-            int s = DUMP;
-            if (i < Lh) {
-                const int sp = slot[h * 256 + i];
-                s = h * U1OFF + sp + (sp >= split ? pad : 0);
-            }
-            if (h == 0) pp0[q] = prod + s; else pp1[q] = prod + s;
+            if (i < L[h]) atomicAdd(&hist[h * 64 + lab[h * 256 + i]], 1);
         }
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const int c = oc[h][k];
-            const bool valid = ov[h][k];
-            int oi = ZERO, oj = ZERO;
-            float sgn = 1.f;
-            bool isb = false;
-            if (valid && c == blank) {                            // Z - (total of stretch 0) - (total of stretch 1)
-                isb = true;
-                sgn = -1.f;
-                if (split > 0) oi = h * U1OFF + split - 1;
-                if (Lh > split) oj = h * U1OFF + Lh + pad - 1;
-            } else if (valid) {
-                // E = last slot of the class (of the nearest present class below it if the class is absent),
-                // pe = slot before its first element (ZERO at the head of a stretch; = E for an absent class)
-                const int st = ctab[h * 128 + c], n = ctab[h * 128 + 64 + c];
-                auto slotpos = [&](int sp) { return h * U1OFF + sp + (sp >= split ? pad : 0); };
-                if (st + n > 0) oi = slotpos(st + n - 1);
-                if (n == 0) oj = oi;
-                else if (!(st == 0 || st == split)) oj = slotpos(st - 1);
-            }
-            pli[2 * h + k] = prod + oi;
-            plj[2 * h + k] = prod + oj;
-            sg[2 * h + k] = sgn;
-            isblank[2 * h + k] = isb;
-        }
-    }
     __syncwarp();
-    // zero pads of the staged rows (emission of unused label slots) and the ZERO slot of the product rows
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int k = 0; k < 2; ++k) nbias[2 * h + k] = (unsigned)hist[h * 64 + oc[h][k]] * 0x4B000000u;
+    const bool isb00 = ov[0][0] && oc[0][0] == blank, isb01 = ov[0][1] && oc[0][1] == blank;
+    const bool isb10 = ov[1][0] && oc[1][0] == blank, isb11 = ov[1][1] && oc[1][1] == blank;
+    __syncwarp();
+    // the occupancy cells start at zero; zero pads of the staged rows (emission of unused label slots)
+    for (int i = lane; i < KF * RW; i += 32) occ[i] = 0u;
     if (lane < KF) {
         rows[lane * RW + zslot0] = 0.f;
         rows[lane * RW + zslot1] = 0.f;
-        prod[lane * RS + ZERO] = 0.f;
     }
     __syncwarp();
 
@@ -617,6 +548,11 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 v = warp_sum(v * pow2i(ea[h] - em));
                 if ((em == E_EMPTY || !(v > 1e-30f) || v > 1e37f) && !flag[h]) flag[h] = 3;
                 if (!flag[h]) {
+                    // P = v * 2^em with v brought into [1, 2): the beta exponents below are tied to P's own exponent,
+                    // so the products alpha*u have mantissas of about 2^-OFF whatever the final lanes' scale was
+                    const int kx = ((__float_as_int(v) >> 23) & 0xff) - 127;
+                    v *= pow2i(-kx);
+                    em += kx;
                     if (lane == 0) {
                         p.nll[bidx[h]] = (float)(-((double)logf(v) + (double)em * 0.69314718055994530942));
                         if (p.status) p.status[bidx[h]] = MDD_ST_OK;
@@ -645,14 +581,9 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
 #pragma unroll
     for (int j = 0; j < NSL; ++j) bt[j] = make_float2(0.f, 0.f);
     int eb[2] = {0, 0};
-    float cst[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) cst[k] = isblank[k] ? zc[k >> 1] : 0.f;
-    // scan role of this lane: frame sf, utterance sh, stretch spart
-    const int sf = lane & (KF - 1), sh = (lane >> 3) & 1, spart = lane >> 4;
-    const int s_split = sh ? st_split[1] : st_split[0], s_pad = sh ? st_pad[1] : st_pad[0], s_L = sh ? L[1] : L[0];
-    const int kb = sh * U1OFF + (spart ? s_split + s_pad : 0);
-    const int ke = sh * U1OFF + (spart ? s_L + s_pad : s_split);
+    constexpr float FIX = 8388608.f * 0.999f;           // fixed-point scale of an occupancy fraction
+    const float2 zs2 = make_float2(zi[0] * FIX, zi[1] * FIX);
+    const float2 magic2 = make_float2(8388608.f, 8388608.f);
     int bad_occ = 0;
 
     // alpha entering chunk j (post-renormalisation) + exponents.  Volatile asm: the loads are issued where they are
@@ -726,7 +657,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
                 if constexpr (REGBUF) A[r][q] = a[2 * q + 1];
-                else reinterpret_cast<float2*>(prod + r * RS)[q * 32 + lane] = a[2 * q + 1];
+                else reinterpret_cast<float2*>(abuf + r * ARS)[q * 32 + lane] = a[2 * q + 1];
             }
         }
         __syncwarp();                                   // the previous chunk's gradient rows have been read
@@ -738,15 +669,14 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
                 if constexpr (REGBUF) al[q] = A[r][q];
-                else al[q] = reinterpret_cast<const float2*>(prod + r * RS)[q * 32 + lane];
+                else al[q] = reinterpret_cast<const float2*>(abuf + r * ARS)[q * 32 + lane];
             }
             beta_step<NSL>(bt, ul, scb, r * RW, bl0, bl1, ep0, ep1, mb);
-            if constexpr (!REGBUF) __syncwarp();          // every lane has read its alpha before the row is reused
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
-                const float2 pl = __fmul2_rn(al[q], ul[q]);
-                pp0[q][r * RS] = pl.x;
-                pp1[q][r * RS] = pl.y;
+                const float2 fx = __ffma2_rn(__fmul2_rn(al[q], ul[q]), zs2, magic2);
+                atomicAdd(reinterpret_cast<unsigned*>(const_cast<float*>(ep0[q])) + (OCCD + r * RW), __float_as_uint(fx.x));
+                atomicAdd(reinterpret_cast<unsigned*>(const_cast<float*>(ep1[q])) + (OCCD + r * RW), __float_as_uint(fx.y));
             }
         }
         if (j > 0) {                                    // pull the next chunk's checkpoint into L2 meanwhile (no register
@@ -756,46 +686,40 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             if (lane < 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(c + 64 * NSL + lane * 32));
         }
         __syncwarp();
-        PT(5)                                           // bwd: beta + product scatter
-        // in-place prefix sums of the sorted products: lane = (frame, utterance, stretch)
-        if (sf < NF) {
-            float* pr = prod + sf * RS;
-            float acc = 0.f;
-            for (int k = kb; k < ke; k += 4) {
-                float4 v = *reinterpret_cast<float4*>(pr + k);
-                acc += v.x; v.x = acc;
-                acc += v.y; v.y = acc;
-                acc += v.z; v.z = acc;
-                acc += v.w; v.w = acc;
-                *reinterpret_cast<float4*>(pr + k) = v;
-            }
-        }
-        __syncwarp();
-        PT(6)                                           // bwd: prefix sums
-        // gradient rows of the chunk: (softmax prob - occupancy / Z) * g
+        PT(5)                                           // bwd: beta + occupancy accumulation
+        // gradient rows of the chunk: (softmax prob - occupancy / Z) * g; the cells are zeroed for the next chunk
         {
             const float g0 = kill0 ? 0.f : g[0], g1 = kill1 ? 0.f : g[1];
-            const float zg0 = zi[0] * g0, zg1 = zi[1] * g1;
-            const float lim0 = kill0 ? -3.0e38f : -1e-3f * zc[0], lim1 = kill1 ? -3.0e38f : -1e-3f * zc[1];
+            const float og0 = g0 * (1.f / FIX), og1 = g1 * (1.f / FIX);
             const bool s00 = act[0] && ov[0][0], s01 = act[0] && ov[0][1], s10 = act[1] && ov[1][0], s11 = act[1] && ov[1][1];
             float* w00 = gr0 + (size_t)t0 * gstride + oc[0][0];
             float* w01 = gr0 + (size_t)t0 * gstride + oc[0][1];
             float* w10 = gr1 + (size_t)t0 * gstride + oc[1][0];
             float* w11 = gr1 + (size_t)t0 * gstride + oc[1][1];
+            constexpr int OMAX = (int)(8388608.0 * 1.002);      // a fraction of Z above 1 (+ rounding): upstream overflow
 #pragma unroll
             for (int r = 0; r < NF; ++r) {
                 const float* d = rows + r * RW;
+                unsigned* oq = occ + r * RW;
                 const float2 pv0 = make_float2(d[lane], d[32 + lane]), pv1 = make_float2(d[CPMAX + lane], d[CPMAX + 32 + lane]);
-                float o[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) o[k] = fmaf(sg[k], pli[k][r * RS], cst[k]) - plj[k][r * RS];
-                // every occupancy must be a number >= 0 up to rounding: catches overflow / NaN anywhere upstream
-                if (!(fminf(o[0], o[1]) >= lim0)) bad_occ |= 1;
-                if (!(fminf(o[2], o[3]) >= lim1)) bad_occ |= 2;
-                if (s00) __stcs(w00, fmaf(-o[0], zg0, pv0.x * g0));
-                if (s01) __stcs(w01, fmaf(-o[1], zg0, pv0.y * g0));
-                if (s10) __stcs(w10, fmaf(-o[2], zg1, pv1.x * g1));
-                if (s11) __stcs(w11, fmaf(-o[3], zg1, pv1.y * g1));
+                int o00 = (int)(oq[lane] - nbias[0]), o01 = (int)(oq[32 + lane] - nbias[1]);
+                int o10 = (int)(oq[CPMAX + lane] - nbias[2]), o11 = (int)(oq[CPMAX + 32 + lane] - nbias[3]);
+                oq[lane] = 0u; oq[32 + lane] = 0u; oq[CPMAX + lane] = 0u; oq[CPMAX + 32 + lane] = 0u;
+                // blank: what the label classes leave of Z
+                const int t0s = __reduce_add_sync(FULL, (ov[0][0] ? o00 : 0) + (ov[0][1] ? o01 : 0));
+                const int t1s = __reduce_add_sync(FULL, (ov[1][0] ? o10 : 0) + (ov[1][1] ? o11 : 0));
+                const int fixi = (int)FIX;
+                if (isb00) o00 = fixi - t0s;
+                if (isb01) o01 = fixi - t0s;
+                if (isb10) o10 = fixi - t1s;
+                if (isb11) o11 = fixi - t1s;
+                // every occupancy must be a fraction of Z in [0, 1] up to rounding: catches overflow / NaN upstream
+                if (!kill0 && ((unsigned)(t0s + 8192) > (unsigned)(OMAX + 8192))) bad_occ |= 1;
+                if (!kill1 && ((unsigned)(t1s + 8192) > (unsigned)(OMAX + 8192))) bad_occ |= 2;
+                if (s00) __stcs(w00, fmaf(-(float)o00, og0, pv0.x * g0));
+                if (s01) __stcs(w01, fmaf(-(float)o01, og0, pv0.y * g0));
+                if (s10) __stcs(w10, fmaf(-(float)o10, og1, pv1.x * g1));
+                if (s11) __stcs(w11, fmaf(-(float)o11, og1, pv1.y * g1));
                 w00 += gstride; w01 += gstride; w10 += gstride; w11 += gstride;
             }
         }
@@ -839,7 +763,7 @@ int env_int(const char* name, int dflt) {
 
 template <int NSL, bool REGBUF, int MAXR>
 int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
-    const PairSmem lay = pair_smem_layout(NSL, PGeo<NSL>::RS, REGBUF);
+    const PairSmem lay = pair_smem_layout(NSL, REGBUF);
     size_t smem = (size_t)lay.total_floats * 4;                  // one warp (= one pair) per CTA
     const int npairs = (p.B + 1) / 2;
     // Warps per SM: the register file allows 8; fewer when that packs the pairs into full waves (a pair runs for the
