@@ -176,7 +176,7 @@ __device__ __forceinline__ void renorm_alpha(float2 (&a)[NSL], int (&ea)[2], flo
 }
 
 struct PairSmem {
-    int occ_off, rows_off, abuf_off, total_floats;
+    int occ_off, rows_off, abuf_off, ckst_off, total_floats;
 };
 __host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf) {
     PairSmem s;
@@ -184,6 +184,7 @@ __host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf) {
     s.occ_off = o; o += KF * RW;                  // class occupancies of the chunk, fixed point (setup scratch too)
     s.rows_off = o; o += KF * RW;                 // exp(lp) rows of the current chunk, both utterances
     s.abuf_off = o; if (!regbuf) o += KF * 32 * NSL;   // alpha label states of the chunk when they do not fit in registers
+    s.ckst_off = o; o += 32 * (2 * NSL + 2);      // the next checkpoint, landing by cp.async (backward sweep)
     s.total_floats = (o + 3) & ~3;
     return s;
 }
@@ -204,6 +205,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     unsigned* occ = reinterpret_cast<unsigned*>(base + lay.occ_off);   // [KF][RW], laid out like the emission rows
     float* rows = base + lay.rows_off;                           // [KF][RW]
     float* abuf = base + lay.abuf_off;                           // [KF][ARS] (!REGBUF)
+    float* ckst = base + lay.ckst_off;                           // [CKW]
     constexpr int OCCD = -KF * RW;                               // occupancy cell of an emission slot: rows -> occ
 
     const int C = p.C, blank = p.blank, T = p.T;
@@ -586,23 +588,34 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     const float2 magic2 = make_float2(8388608.f, 8388608.f);
     int bad_occ = 0;
 
-    // alpha entering chunk j (post-renormalisation) + exponents.  Volatile asm: the loads are issued where they are
-    // written (right after the previous chunk's alpha recomputation), so their latency hides behind beta / scan / rows.
-    auto load_ckpt = [&](int j) {
+    // alpha entering chunk j (post-renormalisation) + exponents travel global -> shared by cp.async, one chunk ahead,
+    // and are picked up with LDS.  Register loads would sit on a scoreboard that the lattice's LDS consumers share
+    // (a warp waits for ALL loads counted on a scoreboard), so every such consumer would wait for their L2 latency.
+    const unsigned ckst_s = (unsigned)__cvta_generic_to_shared(ckst);
+    auto ckpt_issue = [&](int j) {
         const float* c = ck + (size_t)j * CKW;
 #pragma unroll
+        for (int q = 0; q < NSL / 2; ++q)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ckst_s + (q * 32 + lane) * 16), "l"(c + (q * 32 + lane) * 4));
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ckst_s + (64 * NSL + lane * 2) * 4), "l"(c + 64 * NSL + lane * 2));
+        asm volatile("cp.async.commit_group;");
+    };
+    auto ckpt_take = [&]() {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
         for (int q = 0; q < NSL / 2; ++q) {
-            asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];"
-                         : "=f"(a[2 * q].x), "=f"(a[2 * q].y), "=f"(a[2 * q + 1].x), "=f"(a[2 * q + 1].y)
-                         : "l"(c + (q * 32 + lane) * 4));
+            const float4 v = reinterpret_cast<const float4*>(ckst)[q * 32 + lane];
+            a[2 * q] = make_float2(v.x, v.y);
+            a[2 * q + 1] = make_float2(v.z, v.w);
         }
-        asm volatile("ld.global.v2.s32 {%0, %1}, [%2];" : "=r"(ea[0]), "=r"(ea[1]) : "l"(c + 64 * NSL + lane * 2));
+        const int2 e = reinterpret_cast<const int2*>(ckst + 64 * NSL)[lane];
+        ea[0] = e.x; ea[1] = e.y;
     };
 
     auto bwd_chunk = [&](auto nfc, int j, int t0) {
         constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
-        load_ckpt(j);                                   // from L2; lands while the rows are exponentiated
+        ckpt_take();
         if (j < nch - 1) {                              // the last chunk is still staged (and exponentiated)
             __syncwarp();
             commit_rows(nfc, kill0, kill1);
@@ -660,6 +673,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 else reinterpret_cast<float2*>(abuf + r * ARS)[q * 32 + lane] = a[2 * q + 1];
             }
         }
+        if (j > 0) ckpt_issue(j - 1);                   // the alpha registers are free: the next checkpoint sets off
         __syncwarp();                                   // the previous chunk's gradient rows have been read
         PT(4)                                           // bwd: alpha recomputation
         // beta over the chunk; label products alpha_t(s) * u_t(s) into their class-sorted slots
@@ -679,11 +693,19 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 atomicAdd(reinterpret_cast<unsigned*>(const_cast<float*>(ep1[q])) + (OCCD + r * RW), __float_as_uint(fx.y));
             }
         }
-        if (j > 0) {                                    // pull the next chunk's checkpoint into L2 meanwhile (no register
-            const float* c = ck + (size_t)(j - 1) * CKW;    // destination, hence no scoreboard shared with the LDS traffic)
+        if (j >= 2) {                                   // rows two chunks down -> L2 (the next chunk's are in flight)
+            int tq;
+            if (chunk_geom(j - 2, tq)) {
 #pragma unroll
-            for (int q = 0; q < NSL / 2; ++q) asm volatile("prefetch.global.L2 [%0];" ::"l"(c + (q * 32 + lane) * 4));
-            if (lane < 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(c + 64 * NSL + lane * 32));
+                for (int k = 0; k < 2; ++k) {
+                    const int idx = lane + 32 * k;      // 48 tasks: row, utterance, 128-byte part of its 4*C bytes
+                    const int r = idx / 6, u = (idx % 6) / 3, part = idx % 3;
+                    if (idx < 6 * KF) {
+                        const float* q = (u ? lpb1 : lpb0) + (size_t)(tq + r) * p.stride_t + min(part * 32, C - 1);
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+                    }
+                }
+            }
         }
         __syncwarp();
         PT(5)                                           // bwd: beta + occupancy accumulation
@@ -727,6 +749,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     };
 
     if (nch >= 2) load_chunk(nch - 2);
+    ckpt_issue(nch - 1);
     for (int j = nch - 1; j >= 0; --j) {
         int t0;
         if (chunk_geom(j, t0)) bwd_chunk(IC<KF>{}, j, t0);
@@ -772,7 +795,7 @@ int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
     int wps = wps_env;
     if (wps <= 0) {
         double best = 0.0;
-        const int wmax = MAXR >= 255 ? 8 : 12;
+        const int wmax = 65536 / (32 * ((MAXR + 7) & ~7));       // register file
         for (int w = wmax; w >= wmax - 2; --w) {
             const long long slots = (long long)kNumSM * w;
             const double eff = (double)npairs / (double)(((npairs + slots - 1) / slots) * slots);
@@ -802,7 +825,10 @@ template <int NSL>
 int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
     if constexpr (NSL == 8) {
         static int regbuf = env_int("MDD_CTC_PAIR_REGBUF", 1), maxr = env_int("MDD_CTC_PAIR_MAXR", 255);
-        if (regbuf) return launch_cfg<NSL, true, 255>(p, ws, st);
+#ifndef MDD_PAIR_MAXR
+#define MDD_PAIR_MAXR 255
+#endif
+        if (regbuf) return launch_cfg<NSL, true, MDD_PAIR_MAXR>(p, ws, st);
         if (maxr >= 255) return launch_cfg<NSL, false, 255>(p, ws, st);
         return launch_cfg<NSL, false, 168>(p, ws, st);
     }
