@@ -3,8 +3,8 @@
 // Semantics: torch aten ctc_loss / _ctc_loss_backward as reached from nn.CTCLoss at
 // egs/attention_aug/steps/train_ctc.py:186,72,96 and egs/cnn-rnn-ctc/steps/train_ctc.py:148,51,67.
 //
-// The lattice recursion is bound by instruction issue and by shared-memory wavefronts, not by HBM, so
-// this kernel is organised around issuing as few instructions per lattice state as possible:
+// The lattice recursion is bound by per-warp instruction latency and by shared-memory wavefronts, not by HBM (DESIGN.md
+// 5.1), so this kernel is organised around issuing as few instructions per lattice state as possible:
 //
 //  * One warp owns a PAIR of utterances.  Lane l holds NSL consecutive extended-label states of both utterances as
 //    float2 registers (.x = first utterance, .y = second); every lattice update is a packed sm_100 instruction
@@ -22,9 +22,11 @@
 //        occupancy_c / Z = (sum_{s: l'_s = c} alpha u) * (2^OFF / mantissa(P)),  occupancy_blank = Z - sum of labels.
 //  * Ragged pairs: frames [0, min(T0,T1)) are processed jointly, then the longer utterance alone (the other half runs
 //    on zero emissions, stays finite, and its gradient rows are written as zeros).  Chunks never straddle the boundary.
-//  * Class reduction: label products are scattered into a class-sorted row, prefix-summed in place with 128-bit
-//    accesses (lane = frame x utterance x half of the list), class occupancy = P[last] - P[first-1].  No atomics:
-//    results are bitwise reproducible.
+//  * Class reduction: the product of a label state, as a fixed-point fraction of Z, is added with a shared-memory
+//    integer atomic to the cell of its class, which sits at the class's (bank-coloured) emission position; the lane
+//    that owns the position reads it back.  Integer addition is associative: results are bitwise reproducible.
+//  * Loads that travel far never sit on a register scoreboard next to the lattice's LDS traffic: checkpoints come back
+//    by cp.async, log-prob rows are prefetched into L2 two chunks ahead of their register loads.
 //  * Anything unusual (infeasible, empty, malformed, over/underflow) sets flags[b]; ctc_log.cu redoes exactly those
 //    utterances in the same stream with torch's inf / NaN / zero_infinity semantics.
 #include <cstdlib>
