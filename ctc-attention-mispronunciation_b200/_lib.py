@@ -91,7 +91,7 @@ class PostOut(C.Structure):
 
 
 EXPORTS = ["mdd_version", "mdd_error_string", "mdd_launch_count", "mdd_launch_count_reset",
-           "mdd_ctc_loss_workspace_bytes", "mdd_ctc_loss", "mdd_ctc_scale_grad", "mdd_greedy_decode", "mdd_collapse", "mdd_post_align",
+           "mdd_ctc_loss_workspace_bytes", "mdd_ctc_loss", "mdd_ctc_scale_grad", "mdd_greedy_decode", "mdd_collapse", "mdd_post_align", "mdd_corpus_counts",
            "mdd_edit_align_workspace_bytes", "mdd_edit_align", "mdd_beam_search_workspace_bytes", "mdd_beam_search",
            "mdd_exp_transpose", "mdd_prefix_init", "mdd_prefix_score", "mdd_prefix_advance"]
 
@@ -121,6 +121,7 @@ def lib():
     L.mdd_greedy_decode.argtypes = [vp, i, i, i, vp, i, vp, vp, vp, i, vp, vp]
     L.mdd_collapse.argtypes = [vp, i, i, vp, i, vp, vp, i, vp, vp]
     L.mdd_post_align.argtypes = [vp, i, vp, vp, i, vp, i, i, i, vp, i, vp, C.POINTER(PostOut), i, vp]
+    L.mdd_corpus_counts.argtypes = [vp, i, vp, vp, i, vp, i, i, i, i, vp, vp, i, vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp]
     L.mdd_edit_align_workspace_bytes.argtypes = [i, i, i, C.POINTER(sz)]
     L.mdd_edit_align.argtypes = [vp, i, vp, vp, i, vp, i, i, i, vp, vp, i, vp, vp, i, vp, vp, C.POINTER(PostOut), vp,
                                  sz, vp]

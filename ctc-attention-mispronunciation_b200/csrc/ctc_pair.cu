@@ -33,19 +33,13 @@
 #include <type_traits>
 
 #include "common.cuh"
+#include "ctc_lattice.cuh"
 #include "ctc_params.cuh"
 
 namespace mdd {
 namespace {
 
-constexpr int KF = 8;                    // frames per chunk = renormalisation period = checkpoint period
-constexpr int E_EMPTY = -(1 << 20);      // exponent of a lane whose states are all zero
-constexpr int OFF = 50;                  // beta mantissas are kept 2^-OFF below 1 / (alpha mantissa)
-constexpr int CPMAX = 64;                // staged emission row: utterance h at [h*CPMAX, +64): 32 banks x 2 levels
-constexpr int RW = 2 * CPMAX;
-constexpr unsigned FULL = 0xffffffffu;
-template <int N>
-using IC = std::integral_constant<int, N>;
+using namespace lattice;
 
 #ifdef MDD_PAIR_TIMING
 __device__ unsigned long long g_phase_cycles[16];
@@ -57,125 +51,6 @@ __device__ unsigned long long g_phase_cycles[16];
 #define PT(i)
 #define PT_FLUSH
 #endif
-
-template <int NSL>
-struct PGeo {
-    static constexpr int NL = NSL / 2;                     // label states per lane
-    static constexpr int LCAP = 16 * NSL - 1;              // S = 2L+1 <= 32*NSL - 1
-    static constexpr int ARS = 32 * NSL;                   // (!REGBUF) floats per frame of the alpha label-state buffer
-    // mass can cross ceil(2*KF/NSL)+1 lane boundaries between two renormalisations, each multiplying the mantissa by
-    // up to 2^GAP, plus 3^KF of growth: GAP * crossings + 14 < 126
-    static constexpr int GAP = NSL == 2 ? 12 : NSL == 4 ? 22 : NSL == 8 ? 36 : 56;
-    static constexpr int CKW = 32 * (2 * NSL + 2);         // checkpoint words per pair and chunk
-};
-
-__device__ __forceinline__ float pow2i(int x) {            // 2^x, 0 below the normal range, clamped at 2^127
-    return __int_as_float((min(max(x, -127), 127) + 127) << 23);   // branch-free: exponent field 0 is +0.0
-}
-__device__ __forceinline__ float fast_exp(float x) {
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
-    return y;
-}
-__device__ __forceinline__ float fmax3(float a, float b, float c) {
-    float m;
-    asm("max.f32 %0, %1, %2, %3;" : "=f"(m) : "f"(a), "f"(b), "f"(c));
-    return m;
-}
-__device__ __forceinline__ float compc(const float2& v, int h) { return h ? v.y : v.x; }
-
-// ---------------------------------------------------------------------------------------------------------------
-// One lattice step for both utterances.  Lane l owns states s = NSL*l + j; even j = blank, odd j = label (j-1)/2.
-//   alpha: new[s] = (a[s] + a[s-1] + ma * a[s-2]) * e[s]
-//   beta : u[s]   =  b[s] + b[s+1] + mb * b[s+2];  new b[s] = u[s] * e[s]
-// ep0/ep1 point at the emission of my label states inside the staged row of frame 0 (unused slots read a zero).
-// ---------------------------------------------------------------------------------------------------------------
-template <int NSL>
-__device__ __forceinline__ void alpha_step(float2 (&a)[NSL], float2 sc, int roff, const float* __restrict__ bl0,
-                                           const float* __restrict__ bl1, const float* const (&ep0)[NSL / 2],
-                                           const float* const (&ep1)[NSL / 2], const float2 (&ma)[NSL / 2]) {
-    float2 p = make_float2(__shfl_up_sync(FULL, a[NSL - 1].x, 1), __shfl_up_sync(FULL, a[NSL - 1].y, 1));
-    p = __fmul2_rn(p, sc);                                       // sc == 0 on lane 0
-    const float2 eb = make_float2(bl0[roff], bl1[roff]);
-    float2 e[NSL / 2];
-#pragma unroll
-    for (int q = 0; q < NSL / 2; ++q) e[q] = make_float2(ep0[q][roff], ep1[q][roff]);
-    float2 n[NSL];
-#pragma unroll
-    for (int j = 0; j < NSL; ++j) {
-        const float2 m1 = j ? a[j - 1] : p;
-        if (j & 1) {
-            const float2 m2 = j >= 2 ? a[j - 2] : p;
-            n[j] = __fmul2_rn(__ffma2_rn(ma[j >> 1], m2, __fadd2_rn(a[j], m1)), e[j >> 1]);
-        } else {
-            n[j] = __fmul2_rn(__fadd2_rn(a[j], m1), eb);
-        }
-    }
-#pragma unroll
-    for (int j = 0; j < NSL; ++j) a[j] = n[j];
-}
-
-template <int NSL>
-__device__ __forceinline__ void beta_step(float2 (&b)[NSL], float2 (&ul)[NSL / 2], float2 sc, int roff,
-                                          const float* __restrict__ bl0, const float* __restrict__ bl1,
-                                          const float* const (&ep0)[NSL / 2], const float* const (&ep1)[NSL / 2],
-                                          const float2 (&mb)[NSL / 2]) {
-    float2 n0 = make_float2(__shfl_down_sync(FULL, b[0].x, 1), __shfl_down_sync(FULL, b[0].y, 1));
-    float2 n1 = make_float2(__shfl_down_sync(FULL, b[1].x, 1), __shfl_down_sync(FULL, b[1].y, 1));
-    n0 = __fmul2_rn(n0, sc);                                     // sc == 0 on lane 31
-    n1 = __fmul2_rn(n1, sc);
-    const float2 eb = make_float2(bl0[roff], bl1[roff]);
-    float2 e[NSL / 2];
-#pragma unroll
-    for (int q = 0; q < NSL / 2; ++q) e[q] = make_float2(ep0[q][roff], ep1[q][roff]);
-    float2 n[NSL];
-#pragma unroll
-    for (int j = 0; j < NSL; ++j) {
-        const float2 p1 = (j + 1 < NSL) ? b[j + 1] : n0;
-        if (j & 1) {
-            const float2 p2 = (j + 2 < NSL) ? b[j + 2] : n1;
-            const float2 u = __ffma2_rn(mb[j >> 1], p2, __fadd2_rn(b[j], p1));
-            ul[j >> 1] = u;
-            n[j] = __fmul2_rn(u, e[j >> 1]);
-        } else {
-            n[j] = __fmul2_rn(__fadd2_rn(b[j], p1), eb);
-        }
-    }
-#pragma unroll
-    for (int j = 0; j < NSL; ++j) b[j] = n[j];
-}
-
-// Per-lane renormalisation of alpha for both utterances (see the header).  ok[h] = false if utterance h has no
-// alignment mass left or real content had to be squashed by more than 2^100.
-template <int NSL>
-__device__ __forceinline__ void renorm_alpha(float2 (&a)[NSL], int (&ea)[2], float2& sca, int lane, bool (&ok)[2]) {
-    constexpr int GAP = PGeo<NSL>::GAP;
-    float f[2], sc[2];
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        float m = compc(a[0], h);
-#pragma unroll
-        for (int j = 1; j + 1 < NSL; j += 2) m = fmax3(m, compc(a[j], h), compc(a[j + 1], h));
-        m = fmaxf(m, compc(a[NSL - 1], h));
-        const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;
-        const bool some = m >= 1.17549435e-38f && m < 3.0e38f;       // normal, finite (NaN fails both)
-        const int e_own = some ? ea[h] + k : E_EMPTY;
-        int t = e_own + GAP * lane;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) t = max(t, __shfl_up_sync(FULL, t, d));   // lanes < d get their own value back
-        const int e_new = t - GAP * lane;
-        f[h] = pow2i(ea[h] - e_new);
-        ea[h] = e_new;
-        const int e_nb = __shfl_up_sync(FULL, e_new, 1);
-        sc[h] = lane == 0 ? 0.f : pow2i(e_nb - e_new);
-        const bool bad = (m != m) || m >= 3.0e38f || (some && e_new - e_own > 100);
-        ok[h] = __any_sync(FULL, some) && !__any_sync(FULL, bad);
-    }
-    const float2 f2 = make_float2(f[0], f[1]);
-#pragma unroll
-    for (int j = 0; j < NSL; ++j) a[j] = __fmul2_rn(a[j], f2);
-    sca = make_float2(sc[0], sc[1]);
-}
 
 struct PairSmem {
     int occ_off, rows_off, abuf_off, ckst_off, total_floats;
@@ -862,6 +737,8 @@ size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
 
 int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st) {
     float* w = reinterpret_cast<float*>(ws);
+    static int duo = env_int("MDD_CTC_DUO", 0);                  // two warps per pair (ctc_duo.cu)
+    if (duo && ctc_duo_supported(p.C, p.Lmax)) return launch_ctc_duo(p, ws, st);
     switch (pick_nsl(p.Lmax)) {
 #ifndef MDD_PAIR_ONLY8
         case 2: return launch_nsl<2>(p, w, st);

@@ -41,6 +41,8 @@ int launch_ctc_fast(CtcParams p, void* ws, cudaStream_t st);
 
 // two utterances per warp, packed FP32 (ctc_pair.cu): the default fast path
 bool ctc_pair_supported(int C, int Lmax);
+bool ctc_duo_supported(int C, int Lmax);          // two warps per pair (ctc_duo.cu): same workspace as the pair kernel
+int launch_ctc_duo(CtcParams p, void* ws, cudaStream_t st);
 size_t ctc_pair_ws_bytes(int T, int B, int Lmax);
 int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st);
 

@@ -145,6 +145,33 @@ int mdd_post_align(const int32_t* dec, int dec_stride, const int32_t* dec_len, c
                    mdd_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------------------
+ * Corpus MDD evaluation counters.
+ * Replaces: the per-utterance body of test()    egs/attention_aug/steps/test_ctc_nosil.py:218-297
+ *           print_align_space_canonical_origin  egs/attention_aug/steps/test_ctc_nosil.py:33-82 (its dict d)
+ *
+ * lab / dec : human-transcription and recognised token rows (int32, row strides lab_stride / dec_stride) with
+ *             lengths lab_len / dec_len int32[B]; lab_map / dec_map as in mdd_edit_align (id < 0 drops, e.g. 'sil',
+ *             :198-205) -- pass the maps the paths were computed with.
+ * lc_ops    : op paths of wer(labels, canonical) (:219), dc_ops: of wer(decoded, canonical) (:221), both from
+ *             mdd_edit_align with the canonical row as `ref`; uint8 (B, *_stride) with lengths int32[B].
+ * dist_dl   : optional int32[B] = distance of wer(decoded, labels) (:220), copied into counts[.,9] / the totals.
+ * group     : optional uint8[B]; non-zero marks the utterances of the reference's m_speaker list (:152,236).
+ * counts    : int32 (B,12) out = [TA, FR, FA, TR_correct, TR_wrong, n_canonical, FR_m, FA_m, n_labels, dist_dl, 0, 0];
+ *             FR_m / FA_m follow the m_speaker branch, which adds 1 where the general branch adds the list length
+ *             (:270-275).  Rows with status != 0 are zero.
+ * totals    : optional int64[2][12], ACCUMULATED (zero it first): row 0 = sum of counts over all utterances, row 1 =
+ *             over the group with FR/FA taken from FR_m/FA_m (the "mandarin" block, :318-343).
+ * status    : optional int32[B]: MDD_ST_EMPTY where decoder.wer would raise TypeError (an empty side),
+ *             MDD_ST_BADLEN where the two paths disagree about the canonical length.
+ * ------------------------------------------------------------------------------------------------------------------ */
+int mdd_corpus_counts(const int32_t* lab, int lab_stride, const int32_t* lab_len, const int32_t* dec, int dec_stride,
+                      const int32_t* dec_len, int B, int max_lab_len, int max_dec_len, int max_can_len,
+                      const int32_t* lab_map, const int32_t* dec_map, int n_map, const uint8_t* lc_ops, int lc_stride,
+                      const int32_t* lc_len, const uint8_t* dc_ops, int dc_stride, const int32_t* dc_len,
+                      const int32_t* dist_dl, const uint8_t* group, int32_t* counts, int64_t* totals, int32_t* status,
+                      mdd_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------------------
  * CTC prefix beam search with bigram-LM fusion (the reference's joint decoder).
  * Replaces: BeamDecoder.decode -> ctcBeamSearch.decode   utils/ctcDecoder.py:215-226, utils/BeamSearch.py:73-153
  *

@@ -8,7 +8,7 @@ _root = os.path.dirname(os.path.abspath(__file__))
 if _root not in sys.path:
     sys.path.insert(0, _root)
 _pkg = importlib.import_module("ctc-attention-mispronunciation_b200")
-for _sub in ("_lib", "_rt", "loss", "lm", "decoder", "mdd", "prefix", "dist"):
+for _sub in ("_lib", "_rt", "loss", "lm", "decoder", "mdd", "corpus", "prefix", "dist"):
     try:
         _m = importlib.import_module("ctc-attention-mispronunciation_b200." + _sub)
         sys.modules[__name__ + "." + _sub] = _m

@@ -256,6 +256,20 @@ def mdd_post(dec, can, ops):
             "correct": cc, "del_sub": ds}
 
 
+def corpus_counts(lab, lc_ops, dec, dc_ops):
+    """Per-utterance counters of test_ctc_nosil.py:218-293 on integer tokens: lab/dec = human / recognised token
+    lists, lc_ops/dc_ops = op paths of wer(labels, canonical) / wer(decoded, canonical).
+    Returns [TA, FR, FA, TR_correct, TR_wrong, n_canonical, FR_m, FA_m] (the _m pair under the m_speaker rule)."""
+    lab = np.asarray(lab, dtype=np.int32)
+    dec = np.asarray(dec, dtype=np.int32)
+    o1 = np.frombuffer("".join(lc_ops).encode(), dtype=np.uint8).copy()
+    o2 = np.frombuffer("".join(dc_ops).encode(), dtype=np.uint8).copy()
+    cnt = np.zeros(12, np.int32)
+    lib().orc_corpus_counts(_p(lab, C.c_int32), len(lab), _p(o1, C.c_uint8), len(o1), _p(dec, C.c_int32), len(dec),
+                            _p(o2, C.c_uint8), len(o2), _p(cnt, C.c_int32))
+    return [int(x) for x in cnt[:8]]
+
+
 def mdd_score(n_ins, correct, del_sub):
     """infer.py:341-342 (ZeroDivisionError on an empty canonical side, like the reference)."""
     tmp = min(n_ins / 4, 0.1 * (correct + del_sub))

@@ -13,6 +13,8 @@ fixtures next to this script.  What each file pins (reference file:line in paren
   lm_table.npz         LanguageModel.get_bi_prob over the 43-class vocab (utils/NgramLM.py:65-78)
   wer_corpus.json.gz   900-utterance corpora from result/ logs + totals + per-pair wer() outputs
   mdd_post.json.gz     wer -> align_canonical_decoded -> stastics -> score (infer.py:324-342) on 600 noisy pairs + KATs
+  corpus_mdd.json.gz   test_ctc_nosil.py:218-297 (TA/FR/FA/TR counters, PER) per utterance and in total on 500 synthetic
+                       (canonical, human label, recognised) triples; the d maps of print_align_space_canonical_origin
   c1_words.json.gz     BASELINE config 1: the 20 words of egs/vocabulary/single, canonical phones by the rule at
                        infer.py:549-551 from dict/cmudict.dict, synthetic posteriors, greedy + MDD outputs
 """
@@ -395,6 +397,59 @@ def gen_c1(vocab43):
                                "vocab": [vocab45[k] for k in range(45)], "decoded": decoded, "mdd": outs})
 
 
+# ----------------------------------------------------------------------------------------------- corpus MDD evaluation
+def gen_corpus(vocab43):
+    """test_ctc_nosil.py:218-297 executed per utterance (and once over the whole list) on synthetic
+    (canonical, human label, recognised) triples: canonical -> label by L2-style edits, label -> recognised by
+    recogniser noise, with runs of insertions at one position (the remove-while-iterating branch, :276-287)."""
+    D = RL.decoder_module()
+    pr, run = RL.corpus_eval_functions()
+    rng = np.random.default_rng(11)
+    phones = [vocab43[i] for i in range(3, 42)]
+
+    def edit(seq, p_del, p_sub, p_ins, burst):
+        out = []
+        for w in seq:
+            u = rng.random()
+            if u < p_del:
+                pass
+            elif u < p_del + p_sub:
+                out.append(phones[int(rng.integers(0, len(phones)))])
+            else:
+                out.append(w)
+            if rng.random() < p_ins:
+                for _ in range(1 + (int(rng.integers(0, burst)) if burst else 0)):
+                    out.append(phones[int(rng.integers(0, len(phones)))])
+        return out
+
+    utts, labs, cans, decs = [], [], [], []
+    for n in range(500):
+        L = int(rng.integers(1, 14)) if n % 5 else int(rng.integers(14, 60))
+        can = [phones[int(k)] for k in rng.integers(0, len(phones), size=L)]
+        lab = edit(can, 0.06, 0.10, 0.06, 3) or [can[0]]
+        if n % 7 == 0:
+            lab = [phones[int(k)] for k in rng.integers(0, len(phones), size=int(rng.integers(0, 3)))] + lab
+        dec = edit(lab, 0.07, 0.12, 0.08, 3) or [lab[0]]
+        if n % 11 == 0:
+            dec = [phones[int(k)] for k in rng.integers(0, len(phones), size=int(rng.integers(1, 4)))] + dec
+        utts.append(("TXHC_%04d" if n % 3 == 0 else "NJS_%04d") % n)
+        labs.append(" ".join(lab)); cans.append(" ".join(can)); decs.append(" ".join(dec))
+    dec0 = D.Decoder({0: "blank"}, space_idx=-1, blank_index=0)
+    per = []
+    for u, l, c, d in zip(utts, labs, cans, decs):
+        r = run(dec0, [u], [l], [c], [d])
+        _, lc = dec0.wer(l, c)
+        _, dc = dec0.wer(d, c)
+        d1 = pr(l, c, lc)[3]
+        d2 = pr(d, c, dc)[3]
+        per.append({"counts": r, "lc": "".join(lc), "dc": "".join(dc),
+                    "d1": [[str(k), v] for k, v in d1.items()], "d2": [[str(k), v] for k, v in d2.items()]})
+    total = run(dec0, utts, labs, cans, decs)
+    jdump("corpus_mdd.json.gz", {"utt": utts, "labels": labs, "canonicals": cans, "decoded": decs, "per_utt": per,
+                                 "total": total, "m_speaker": ["TXHC"]})
+    print("corpus_mdd", total)
+
+
 def main():
     assert RL.available(), "reference tree not mounted"
     os.makedirs(os.path.join(GOLD, "assets"), exist_ok=True)
@@ -402,12 +457,13 @@ def main():
     shutil.copy(RL.arpa_path(), os.path.join(GOLD, "assets", "lm_phone_bg.arpa"))
     vocab43 = RL.units_vocab()
     assert len(vocab43) == 43, len(vocab43)
-    steps = sys.argv[1:] or ["ctc", "greedy", "beam_small", "beam_c4", "lm", "wer", "mdd", "c1"]
+    steps = sys.argv[1:] or ["ctc", "greedy", "beam_small", "beam_c4", "lm", "wer", "mdd", "c1", "corpus"]
     for s in steps:
         print("==", s, flush=True)
         {"ctc": gen_ctc, "greedy": lambda: gen_greedy(vocab43), "beam_small": lambda: gen_beam_small(vocab43),
          "beam_c4": lambda: gen_beam_c4(vocab43), "lm": lambda: gen_lm_table(vocab43), "wer": gen_wer_corpus,
-         "mdd": lambda: gen_mdd_post(vocab43), "c1": lambda: gen_c1(vocab43)}[s]()
+         "mdd": lambda: gen_mdd_post(vocab43), "c1": lambda: gen_c1(vocab43),
+         "corpus": lambda: gen_corpus(vocab43)}[s]()
 
 
 if __name__ == "__main__":

@@ -20,6 +20,8 @@
  *                             (+ calcExtPr :52-66, log_add_prob :43-50, BeamState.sort/norm :23-33)
  *   orc_mdd_post              align_canonical_decoded / stastics / score
  *                             egs/attention_aug/infer.py:162-209, 405-433, 338-342
+ *   orc_corpus_counts         TA/FR/FA/TR counters of the corpus MDD evaluation
+ *                             egs/attention_aug/steps/test_ctc_nosil.py:218-293 (+ :33-82)
  *   orc_prefix_score          CTC prefix scorer for CTC/attention joint decoding.  NOT in the reference
  *                             (Watanabe et al. 2017 formulation): parity unpinned
  *                             by the reference; pinned by the psi(l.eos) == -nll invariant against
@@ -456,6 +458,69 @@ ORC_API int orc_mdd_post(const int32_t* dec, int Ld, const int32_t* can, int Lc,
         }
     }
     counts[0] = m; counts[1] = ni; counts[2] = ns; counts[3] = nd; counts[4] = cc; counts[5] = ds;
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * 5b. Corpus MDD evaluation: the per-utterance body of egs/attention_aug/steps/test_ctc_nosil.py:218-293
+ *     over integer tokens.  lc_ops = path of wer(labels, canonical), dc_ops = path of wer(decoded, canonical)
+ *     (both against the same canonical row, so both hold the same number of non-'I' ops = canonical phones).
+ *     print_align_space_canonical_origin (:33-82) turns a path into d[j] for every canonical position j
+ *     ('-' | 'S'+hyp phone | 'D') and d['I'] = [str(j-1)+str(j) per insertion]; for consecutive integers that
+ *     string determines j, so the lists hold j itself.  The 'I' branch (:265-287) removes from both lists
+ *     WHILE iterating over the first (Python skips the element that slides into the freed index): restated
+ *     literally.  counts[12] = TA, FR, FA, TR-correct, TR-wrong, n_canonical, FR and FA under the m_speaker
+ *     rule (:270-275 add 1 instead of the list length), 0...
+ * ---------------------------------------------------------------------------------------------- */
+static int orc_list_find(const int* a, int n, int v) { for (int i = 0; i < n; ++i) if (a[i] == v) return i; return -1; }
+static void orc_list_remove(int* a, int* n, int at) { for (int i = at; i + 1 < *n; ++i) a[i] = a[i + 1]; --*n; }
+/* d code: 0 '-', 1 'D', 2 + token 'S'+token */
+static int orc_dmap(const int32_t* hyp, int Lh, const uint8_t* ops, int n, int* d, int* ilist) {
+    int i = 0, j = 0, ni = 0;
+    for (int k = 0; k < n; ++k) {
+        if (ops[k] == '-') { d[j++] = 0; ++i; }
+        else if (ops[k] == 'S') { d[j++] = 2 + (i < Lh ? hyp[i] : -1); ++i; }
+        else if (ops[k] == 'D') { d[j++] = 1; }
+        else { ilist[ni++] = j; ++i; }
+    }
+    return ni;
+}
+ORC_API int orc_corpus_counts(const int32_t* lab, int Ll, const uint8_t* lc_ops, int n_lc,
+                              const int32_t* dec, int Ld, const uint8_t* dc_ops, int n_dc, int32_t* counts) {
+    int* d1 = (int*)malloc(sizeof(int) * (size_t)(n_lc + n_dc + 2) * 4);
+    int* d2 = d1 + (n_lc + n_dc + 2);
+    int* i1 = d2 + (n_lc + n_dc + 2);
+    int* i2 = i1 + (n_lc + n_dc + 2);
+    int n1 = orc_dmap(lab, Ll, lc_ops, n_lc, d1, i1);
+    int n2 = orc_dmap(dec, Ld, dc_ops, n_dc, d2, i2);
+    int Lc = n_lc - n1;                       /* canonical positions */
+    int ta = 0, fr = 0, fa = 0, trc = 0, trw = 0;
+    for (int k = 0; k < Lc; ++k) {
+        if (d1[k] == 0 && d2[k] == 0) ++ta;
+        else if (d1[k] == 0) ++fr;
+        else if (d2[k] == 0) ++fa;
+        else if (d1[k] == d2[k]) ++trc;
+        else ++trw;
+    }
+    int m_fr = fr, m_fa = fa;
+    if (n1 && !n2) { fa += n1; m_fa += 1; }
+    else if (!n1 && n2) { fr += n2; m_fr += 1; }
+    else if (n1 && n2) {
+        for (int idx = 0; idx < n1; ++idx) {                  /* for e in d1['I'] (live list) */
+            int e = i1[idx];
+            int at2 = orc_list_find(i2, n2, e);
+            if (at2 >= 0) {
+                orc_list_remove(i1, &n1, orc_list_find(i1, n1, e));
+                orc_list_remove(i2, &n2, at2);
+                ++trc;
+            }
+        }
+        fa += n1; fr += n2; m_fa += n1; m_fr += n2;
+    }
+    counts[0] = ta; counts[1] = fr; counts[2] = fa; counts[3] = trc; counts[4] = trw; counts[5] = Lc;
+    counts[6] = m_fr; counts[7] = m_fa;
+    for (int k = 8; k < 12; ++k) counts[k] = 0;
+    free(d1);
     return 0;
 }
 

@@ -8,6 +8,8 @@ tests, which skip when the tree is absent.
 * ``infer.py`` cannot be imported (argparse at import time, infer.py:58; missing third-party deps), so its pure
   functions are AST-extracted and exec'd: align_canonical_decoded (:162-209), stastics (:405-433),
   print_aligned_string (:155-160).
+* ``steps/test_ctc_nosil.py`` likewise: print_align_space_canonical_origin (:33-82) and the counter loop of
+  ``test()`` (:218-297) are extracted and exec'd (corpus_eval_functions).
 """
 from __future__ import annotations
 
@@ -62,6 +64,50 @@ def infer_functions():
     exec(compile(ast.Module(body=body, type_ignores=[]), "infer.py", "exec"), ns)
     _cache["infer"] = {k: ns[k] for k in want}
     return _cache["infer"]
+
+
+def corpus_eval_functions():
+    """(print_align_space_canonical_origin, run_loop) from egs/attention_aug/steps/test_ctc_nosil.py.
+
+    The module cannot be imported (yaml config, kaldiio data loader, model checkpoint), so the helper (:33-82) is
+    AST-extracted and the counter loop -- the statement ``for x in range(len(labels_nosil)):`` inside ``test()``
+    (:218-297) -- is extracted AS A STATEMENT and exec'd over a namespace holding the variables it reads.
+    ``run_loop(decoder, utt_list, labels_nosil, canonicals_nosil, decoded_nosil, m_speaker)`` returns the counters
+    the reference prints afterwards (:299-343)."""
+    if "corpus" in _cache:
+        return _cache["corpus"]
+    import contextlib
+    import io
+    src = open(os.path.join(eg_dir(), "steps", "test_ctc_nosil.py")).read()
+    tree = ast.parse(src)
+    helper = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "print_align_space_canonical_origin"]
+    test_fn = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "test"][0]
+    loops = [n for n in ast.walk(test_fn) if isinstance(n, ast.For) and isinstance(n.target, ast.Name) and
+             n.target.id == "x" and "labels_nosil" in ast.dump(n.iter)]
+    assert len(helper) == 1 and len(loops) == 1
+    ns = {}
+    exec(compile(ast.Module(body=helper, type_ignores=[]), "test_ctc_nosil.py", "exec"), ns)
+    loop_code = compile(ast.Module(body=loops, type_ignores=[]), "test_ctc_nosil.py", "exec")
+    names = ["true_accept", "false_rejection", "false_accept", "true_rejection_correct_diagnose",
+             "true_rejection_wrong_diagnose", "total_phonemes_in_canonical", "total_wer"]
+
+    def run_loop(decoder, utt_list, labels_nosil, canonicals_nosil, decoded_nosil, m_speaker=("TXHC",)):
+        env = dict(ns)
+        env.update({k: 0 for k in names})
+        env.update({"m_" + k: 0 for k in names[:-1]})
+        env.update({"m_wer": 0, "m_decoder_num": 0, "m_speaker": list(m_speaker), "decoder": decoder,
+                    "utt_list": utt_list, "labels_nosil": labels_nosil, "canonicals_nosil": canonicals_nosil,
+                    "decoded_nosil": decoded_nosil, "test_wrd_dict": {u: "" for u in utt_list}})
+        decoder.num_word = 0
+        with contextlib.redirect_stdout(io.StringIO()):
+            exec(loop_code, env)
+        out = {k: env[k] for k in names}
+        out.update({"m_" + k: env["m_" + k] for k in names[:-1]})
+        out.update({"m_wer": env["m_wer"], "m_decoder_num": env["m_decoder_num"], "num_word": decoder.num_word})
+        return out
+
+    _cache["corpus"] = (ns["print_align_space_canonical_origin"], run_loop)
+    return _cache["corpus"]
 
 
 def units_vocab(eg="attention_aug"):

@@ -508,3 +508,96 @@ def test_prefix_scorer_vs_oracle_and_invariant(M):
         nll = torch.nn.functional.ctc_loss(x[:, b:b + 1].double(), torch.tensor([labels[b]]), lens[b:b + 1],
                                            torch.tensor([len(labels[b])]), reduction="none")
         assert abs(float(eos[b, 0]) + float(nll)) < 1e-4 * max(1.0, abs(float(nll)))
+
+
+# ----------------------------------------------------------------------------------------------------- corpus MDD evaluation
+CORPUS_KEYS = ["true_accept", "false_rejection", "false_accept", "true_rejection_correct_diagnose",
+               "true_rejection_wrong_diagnose", "total_phonemes_in_canonical"]
+
+
+def test_corpus_mdd_vs_reference_golden(M):
+    """test_ctc_nosil.py:218-343 executed by the real reference on 500 triples (tests/golden/corpus_mdd.json.gz):
+    per-utterance counters, m_speaker block, PER numerators and corpus totals, bit-exact."""
+    from mddctc.corpus import CorpusMDD
+    data = jload("corpus_mdd.json.gz")
+    ev = CorpusMDD({0: "blank"}, m_speaker=data["m_speaker"])
+    r = ev.evaluate_strings(data["utt"], data["labels"], data["canonicals"], data["decoded"])
+    counts = r["counts"].cpu().numpy()
+    for b, ref in enumerate(data["per_utt"]):
+        want, c = ref["counts"], counts[b].tolist()
+        assert c[:6] == [want[k] for k in CORPUS_KEYS], (b, c, want)
+        assert c[9] == want["total_wer"] and c[8] == want["num_word"]
+        if data["utt"][b][:4] in data["m_speaker"]:
+            assert [c[0], c[6], c[7], c[3], c[4], c[5]] == [want["m_" + k] for k in CORPUS_KEYS], (b, c, want)
+        n = int(r["lc"]["ops_len"][b])
+        assert bytes(r["lc"]["ops"][b, :n].cpu().numpy()).decode() == ref["lc"]
+    s = ev.summary()
+    tot = data["total"]
+    for k in CORPUS_KEYS + ["total_wer", "num_word"]:
+        assert s[k] == tot[k], k
+    for k in CORPUS_KEYS:
+        assert s["m_" + k] == tot["m_" + k], k
+    assert s["m_total_wer"] == tot["m_wer"] and s["m_num_word"] == tot["m_decoder_num"]
+    tr = tot["true_rejection_correct_diagnose"] + tot["true_rejection_wrong_diagnose"]
+    assert s["precision"] == float(tr) / (tr + tot["false_rejection"]) * 100
+    assert s["recall"] == float(tr) / (tr + tot["false_accept"]) * 100
+    with pytest.raises(TypeError):
+        ev.evaluate_strings(["X"], ["sil"], ["a b"], ["a"])
+
+
+def test_corpus_mdd_random_vs_oracle(M):
+    """Class-id rows with 'sil' inside, long rows, bursts of insertions at one canonical position."""
+    from mddctc.corpus import CorpusMDD
+    rng = np.random.default_rng(21)
+    vocab = {i: ("sil" if i == 2 else "p%d" % i) for i in range(12)}
+    ev = CorpusMDD(vocab)
+    for (B, Lc, V) in ((257, 12, 5), (64, 150, 11), (33, 400, 4)):
+        def noisy(rows, p):
+            out = []
+            for r in rows:
+                o = []
+                for w in r:
+                    u = rng.random()
+                    if u < p:
+                        continue
+                    o.append(int(rng.integers(1, V + 1)) if u < 2 * p else w)
+                    while rng.random() < p:
+                        o.append(int(rng.integers(1, V + 1)))
+                out.append(o or [3])
+            return out
+        can = [[int(x) for x in rng.integers(1, V + 1, size=int(rng.integers(1, Lc + 1)))] for _ in range(B)]
+        for r in can:
+            if all(w == 2 for w in r):
+                r[0] = 3
+        lab = noisy(can, 0.12)
+        dec = noisy(lab, 0.15)
+        for rows in (lab, dec):
+            for r in rows:
+                if all(w == 2 for w in r):
+                    r.append(4)
+        grp = (rng.random(B) < 0.4).astype(np.uint8)
+
+        def pack(rows):
+            n = max(len(r) for r in rows)
+            A = np.zeros((B, n), dtype=np.int32)
+            for i, r in enumerate(rows):
+                A[i, :len(r)] = r
+            return torch.from_numpy(A).cuda(), torch.tensor([len(r) for r in rows], dtype=torch.int32).cuda()
+        (D, dl), (Lb, ll), (Cn, cl) = pack(dec), pack(lab), pack(can)
+        ev.reset()
+        r = ev.evaluate_tokens(D, dl, Lb, ll, Cn, cl, group=torch.from_numpy(grp).cuda())
+        got = r["counts"].cpu().numpy()
+        assert int(r["status"].abs().sum()) == 0
+        f = lambda rows: [[w for w in q if w != 2] for q in rows]
+        fl, fc, fd = f(lab), f(can), f(dec)
+        _, lc, _ = O.edit_align(fl, fc)
+        dd, _, _ = O.edit_align(fd, fl)
+        _, dc, _ = O.edit_align(fd, fc)
+        tot = np.zeros((2, 12), dtype=np.int64)
+        for b in range(B):
+            c = O.corpus_counts(fl[b], lc[b], fd[b], dc[b]) + [len(fl[b]), int(dd[b]), 0, 0]
+            assert got[b].tolist() == c, (b, got[b].tolist(), c)
+            tot[0] += c
+            if grp[b]:
+                tot[1] += [c[0], c[6], c[7]] + c[3:]
+        assert np.array_equal(ev.totals, tot)

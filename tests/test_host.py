@@ -84,6 +84,19 @@ def test_mdd_scorer_maps(M):
         mdd_score(0, 0, 0)
 
 
+def test_print_align_space_canonical_origin_mirror(M):
+    """Host mirror of test_ctc_nosil.py:33-82 against the d maps and printed rows the real reference produced."""
+    from mddctc.corpus import print_align_space_canonical_origin as pr
+    data = jload("corpus_mdd.json.gz")
+    for b, ref in enumerate(data["per_utt"]):
+        c = data["canonicals"][b]
+        for s1, path, want in ((data["labels"][b], ref["lc"], ref["d1"]), (data["decoded"][b], ref["dc"], ref["d2"])):
+            r = pr(s1, c, list(path))
+            assert [[str(k), v] for k, v in r[3].items()] == want
+            assert len(r[0].split()) == len(path) == len(r[1].split())
+    assert pr("a bb ccc", "a dd", ["-", "S", "I"])[:3] == ("a   dd  I  ", "a   bb  ccc", "-   S   I  ")
+
+
 def test_shard_helpers(M):
     from mddctc.dist import balanced_buckets, shard_bounds
     for n in (0, 1, 7, 4096):

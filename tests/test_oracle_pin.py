@@ -155,3 +155,46 @@ def test_prefix_score_invariants():
         nll = torch.nn.functional.ctc_loss(x[:, None, :], torch.tensor([labels]), torch.tensor([T]),
                                            torch.tensor([len(labels)]), reduction="none")
         assert abs(eos + float(nll)) < 1e-10
+
+
+def _corpus_rows(data):
+    words = {}
+    enc = lambda s: [words.setdefault(w, len(words)) for w in s.split()]
+    return [enc(s) for s in data["labels"]], [enc(s) for s in data["canonicals"]], [enc(s) for s in data["decoded"]]
+
+
+def test_corpus_counts_oracle_vs_reference():
+    """test_ctc_nosil.py:218-297 executed by oracle/gen_golden.py on 500 triples: per-utterance counters (both the
+    general and the m_speaker rule), paths, PER numerators, and the corpus totals."""
+    data = jload("corpus_mdd.json.gz")
+    lab, can, dec = _corpus_rows(data)
+    _, lc, st1 = O.edit_align(lab, can)
+    dl, _, st2 = O.edit_align(dec, lab)
+    _, dc, st3 = O.edit_align(dec, can)
+    assert not (st1.any() or st2.any() or st3.any())
+    keys = ["true_accept", "false_rejection", "false_accept", "true_rejection_correct_diagnose",
+            "true_rejection_wrong_diagnose", "total_phonemes_in_canonical"]
+    tot = {k: 0 for k in keys + ["total_wer", "num_word"]}
+    quirk = 0
+    for b, ref in enumerate(data["per_utt"]):
+        assert "".join(lc[b]) == ref["lc"] and "".join(dc[b]) == ref["dc"]
+        c = O.corpus_counts(lab[b], lc[b], dec[b], dc[b])
+        want = ref["counts"]
+        assert c[:6] == [want[k] for k in keys], (b, c, want)
+        assert int(dl[b]) == want["total_wer"] and len(lab[b]) == want["num_word"]
+        if data["utt"][b][:4] in data["m_speaker"]:
+            assert [c[0], c[6], c[7], c[3], c[4], c[5]] == [want["m_" + k] for k in keys], (b, c, want)
+            quirk += c[6] != c[1] or c[7] != c[2]
+        for k, v in zip(keys, c[:6]):
+            tot[k] += v
+        tot["total_wer"] += int(dl[b])
+        tot["num_word"] += len(lab[b])
+    assert quirk > 0                                                    # the m_speaker '+= 1' branch is exercised
+    for k, v in tot.items():
+        assert v == data["total"][k], k
+
+
+def test_corpus_insertion_keys_unique():
+    """print_align_space_canonical_origin keys an insertion by str(j-1)+str(j) (:61); the oracle stores j."""
+    keys = [str(j - 1) + str(j) for j in range(0, 5000)]
+    assert len(set(keys)) == len(keys)
