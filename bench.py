@@ -358,7 +358,57 @@ def run_extras(dev):
                                        "config": "ragged T 50-1500, B=2048, C=43, greedy decode + Levenshtein/MDD alignment"}
     except Exception as e:          # noqa
         out["greedy_mdd_utt_per_s"] = {"error": str(e)[:200]}
+    del lp2
+    try:
+        out["ctc_from_logits"] = run_logits_extra(dev)
+    except Exception as e:          # noqa
+        out["ctc_from_logits"] = {"error": str(e)[:200]}
     return out
+
+
+def run_logits_extra(dev, steps=10):
+    """SURVEY 8f rank 1 at the config-3 shape: logits in, logit gradient out.  Fused = mdd_ctc_loss_logits (row-LSE
+    pre-pass + CTC kernel); unfused = torch log_softmax -> mdd_ctc_loss -> torch log_softmax backward on the same GPU."""
+    from mddctc.loss import ctc_loss_raw, row_lse
+    T, B, C, L = 1000, 4096, 42, 120
+    g = torch.Generator(device=dev).manual_seed(5)
+    x = torch.randn(T, B, C, device=dev, generator=g) * 2
+    tg = torch.randint(1, C, (B, L), device=dev, generator=g)
+    il = torch.full((B,), T, dtype=torch.int64, device=dev)
+    tl = torch.full((B,), L, dtype=torch.int64, device=dev)
+    nll = torch.empty(B, device=dev)
+    grad = torch.empty((T, B, C), device=dev)
+    st = torch.empty(B, dtype=torch.int32, device=dev)
+    lse = torch.empty((T, B), device=dev)
+    am = torch.empty((T, B), dtype=torch.uint8, device=dev)
+
+    def fused():
+        ctc_loss_raw(x, tg, il, tl, validate=False, nll=nll, grad=grad, status=st, logits=True, row_lse=lse, argmax=am)
+
+    def unfused():
+        lp = torch.log_softmax(x, -1)
+        ctc_loss_raw(lp, tg, il, tl, validate=False, nll=nll, grad=grad, status=st)
+        return torch.ops.aten._log_softmax_backward_data(grad, lp, -1, torch.float32)
+
+    def prepass():
+        row_lse(x, want_argmax=True)
+
+    res = {}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for name, fn in (("fused_ms", fused), ("unfused_ms", unfused), ("row_lse_prepass_ms", prepass)):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        res[name] = e0.elapsed_time(e1) / steps
+    res["fused_frames_per_s"] = T * B / (res["fused_ms"] * 1e-3)
+    res["row_lse_prepass_gbs"] = (T * B * (4 * C + 5)) / (res["row_lse_prepass_ms"] * 1e-3) / 1e9
+    res["config"] = "config-3 shape, logits (T,B,C) in, logit gradient out; unfused = torch log_softmax + mdd_ctc_loss + torch log_softmax backward"
+    return res
 
 
 def main():

@@ -57,11 +57,14 @@ extern "C" int mdd_ctc_loss_workspace_bytes(int T, int B, int C, int max_target_
     return MDD_OK;
 }
 
-extern "C" int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t stride_t, int64_t stride_b,
-                            const int64_t* targets, int64_t tgt_stride, const int64_t* input_lengths,
-                            const int64_t* target_lengths, int max_target_len, int blank, int zero_infinity,
-                            const float* grad_out, float grad_out_scalar, float* nll, float* grad, float* loss_sum,
-                            int32_t* status, int algo, void* workspace, size_t workspace_bytes, mdd_stream_t stream) {
+namespace {
+// row_lse == null: `log_probs` holds log-probs; else it holds logits and row_lse (T*B) receives their row log-sum-exp
+int ctc_loss_impl(const float* log_probs, int T, int B, int C, int64_t stride_t, int64_t stride_b,
+                  const int64_t* targets, int64_t tgt_stride, const int64_t* input_lengths,
+                  const int64_t* target_lengths, int max_target_len, int blank, int zero_infinity,
+                  const float* grad_out, float grad_out_scalar, float* nll, float* grad, float* loss_sum,
+                  int32_t* status, float* row_lse, uint8_t* argmax, int algo, void* workspace,
+                  size_t workspace_bytes, mdd_stream_t stream) {
     if (T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || blank < 0 || blank >= C || algo < 0 ||
         algo > 3)
         return MDD_E_ARG;
@@ -75,7 +78,7 @@ extern "C" int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t
     unsigned char* ws = (unsigned char*)workspace;
 
     CtcParams p{};
-    p.lp = log_probs; p.T = T; p.B = B; p.C = C; p.stride_t = stride_t; p.stride_b = stride_b;
+    p.lp = log_probs; p.lse = row_lse; p.T = T; p.B = B; p.C = C; p.stride_t = stride_t; p.stride_b = stride_b;
     p.targets = targets; p.tgt_stride = tgt_stride; p.in_len = input_lengths; p.tgt_len = target_lengths;
     p.Lmax = max_target_len; p.blank = blank; p.zero_inf = zero_infinity;
     p.grad_out = grad_out; p.gscalar = grad_out_scalar; p.nll = nll; p.grad = grad; p.status = status;
@@ -87,8 +90,13 @@ extern "C" int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t
         rc = launch_tgt_offsets(target_lengths, B, reinterpret_cast<int64_t*>(ws + w.off_offsets), st);
         if (rc) return rc;
     }
-    const int kern = T > 0 ? ctc_kernel_choice(C, max_target_len, algo) : 0;
+    int kern = T > 0 ? ctc_kernel_choice(C, max_target_len, algo) : 0;
     if (algo == 2 && kern != 1) return MDD_E_UNSUPPORTED;
+    if (row_lse) {
+        if (kern == 2) kern = 0;                                 // the scalar kernel reads log-probs only
+        rc = launch_row_lse(log_probs, T, B, C, stride_t, stride_b, row_lse, argmax, st);
+        if (rc) return rc;
+    }
     if (kern) {
         // flags[b] != 0 on return -> utterance needs the log-space path
         rc = kern == 2 ? launch_ctc_fast(p, ws + w.off_fast, st) : launch_ctc_pair(p, ws + w.off_fast, st);
@@ -108,6 +116,30 @@ extern "C" int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t
         if (rc) return rc;
     }
     return MDD_OK;
+}
+}  // namespace
+
+extern "C" int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t stride_t, int64_t stride_b,
+                            const int64_t* targets, int64_t tgt_stride, const int64_t* input_lengths,
+                            const int64_t* target_lengths, int max_target_len, int blank, int zero_infinity,
+                            const float* grad_out, float grad_out_scalar, float* nll, float* grad, float* loss_sum,
+                            int32_t* status, int algo, void* workspace, size_t workspace_bytes, mdd_stream_t stream) {
+    return ctc_loss_impl(log_probs, T, B, C, stride_t, stride_b, targets, tgt_stride, input_lengths, target_lengths,
+                         max_target_len, blank, zero_infinity, grad_out, grad_out_scalar, nll, grad, loss_sum, status,
+                         nullptr, nullptr, algo, workspace, workspace_bytes, stream);
+}
+
+extern "C" int mdd_ctc_loss_logits(const float* logits, int T, int B, int C, int64_t stride_t, int64_t stride_b,
+                                   const int64_t* targets, int64_t tgt_stride, const int64_t* input_lengths,
+                                   const int64_t* target_lengths, int max_target_len, int blank, int zero_infinity,
+                                   const float* grad_out, float grad_out_scalar, float* nll, float* grad_logits,
+                                   float* loss_sum, int32_t* status, float* row_lse, uint8_t* argmax, int algo,
+                                   void* workspace, size_t workspace_bytes, mdd_stream_t stream) {
+    if (!row_lse && (long long)T * B > 0) return MDD_E_ARG;
+    if (algo == 3) return MDD_E_UNSUPPORTED;
+    return ctc_loss_impl(logits, T, B, C, stride_t, stride_b, targets, tgt_stride, input_lengths, target_lengths,
+                         max_target_len, blank, zero_infinity, grad_out, grad_out_scalar, nll, grad_logits, loss_sum,
+                         status, row_lse, argmax, algo, workspace, workspace_bytes, stream);
 }
 
 extern "C" int mdd_ctc_scale_grad(float* grad, int T, int B, int C, const float* scale, float scalar,

@@ -549,7 +549,7 @@ __device__ __forceinline__ void lattice_role(const CtcParams& p, float* ckpt_ws,
         set_buf(b);
         {
             bool ok[2];
-            renorm_alpha<NSL>(a, ea, sca, lane, ok);
+            renorm_alpha<NSL>(a, ea, sca, lane, ok, true);
             if (!ok[0] && !kill0 && !flag[0]) flag[0] = 2 | (t0 << 8);
             if (!ok[1] && !kill1 && !flag[1]) flag[1] = 2 | (t0 << 8);
         }
@@ -691,7 +691,7 @@ __device__ __forceinline__ void lattice_role(const CtcParams& p, float* ckpt_ws,
 #pragma unroll
         for (int r = NF - 1; r >= 0; --r) {
             float2 ul[NL];
-            beta_step<NSL>(bt, ul, scb, r * RW, bl0, bl1, ep0, ep1, mb);
+            beta_step<NSL>(bt, ul, scb, make_float2(1.f, 1.f), r * RW, bl0, bl1, ep0, ep1, mb);
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
                 const float2 fx = __ffma2_rn(__fmul2_rn(A[r][q], ul[q]), zs2, magic2);

@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
     float* ck = p.ckpt + (size_t)b * p.n_ckpt * Smax;
 
     // ------------------------------------------------------------------ forward: alpha, checkpoints, nll
-    if (tid < C) srow[tid] = lp_b[tid];
+    if (tid < C) srow[tid] = lp_b[tid] - (p.lse ? p.lse[b] : 0.f);
     __syncthreads();
     {
         float pm = -CUDART_INF_F;
@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
     double shift_sum = 0.0;                  // identical in every thread
     for (int t = 1; t < Tb; ++t) {
         float* rw = srow + (t & 1) * C;
-        if (tid < C) rw[tid] = lp_b[(size_t)t * p.stride_t + tid];
+        if (tid < C) rw[tid] = lp_b[(size_t)t * p.stride_t + tid] - (p.lse ? p.lse[(size_t)t * p.B + b] : 0.f);
         __syncthreads();
         const float shift = row_shift((t - 1) & 1);
         shift_sum += (double)shift;
@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
         }
         for (int t = t0 + 1; t < t1; ++t) {
             float* rw = srow + (t & 1) * C;
-            if (tid < C) rw[tid] = lp_b[(size_t)t * p.stride_t + tid];
+            if (tid < C) rw[tid] = lp_b[(size_t)t * p.stride_t + tid] - (p.lse ? p.lse[(size_t)t * p.B + b] : 0.f);
             __syncthreads();
             const float shift = row_shift((t - 1) & 1);
             const float* prev = chunk + (size_t)(t - 1 - t0) * Smax;
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(NT) ctc_log_kernel(CtcParams p) {
         __syncthreads();   // s_pmax is reused (with its own parity) by the beta sweep
         for (int t = t1 - 1; t >= t0; --t) {
             float* rw = srow + (t & 1) * C;
-            if (tid < C) rw[tid] = lp_b[(size_t)t * p.stride_t + tid];
+            if (tid < C) rw[tid] = lp_b[(size_t)t * p.stride_t + tid] - (p.lse ? p.lse[(size_t)t * p.B + b] : 0.f);
             __syncthreads();
             const float* al = chunk + (size_t)(t - t0) * Smax;
             float* bn = bbuf + (t & 1) * Smax;

@@ -29,6 +29,7 @@
 //    by cp.async, log-prob rows are prefetched into L2 two chunks ahead of their register loads.
 //  * Anything unusual (infeasible, empty, malformed, over/underflow) sets flags[b]; ctc_log.cu redoes exactly those
 //    utterances in the same stream with torch's inf / NaN / zero_infinity semantics.
+#include <cstdio>
 #include <cstdlib>
 #include <type_traits>
 
@@ -66,7 +67,7 @@ __host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf) {
     return s;
 }
 
-template <int NSL, bool REGBUF, int MAXR>
+template <int NSL, bool REGBUF, int MAXR, bool LOGITS>
 __global__ void __maxnreg__(MAXR)
 ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     using G = PGeo<NSL>;
@@ -294,6 +295,11 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     for (int h = 0; h < 2; ++h) g[h] = act[h] ? (p.grad_out ? p.grad_out[bidx[h]] : 1.f) * p.gscalar : 0.f;
 
     float2 pre0[KF], pre1[KF];                          // the next chunk's rows, in flight
+    // LOGITS: lane r holds -lse * log2(e) of row r of the first utterance, lane KF + r of the second; the row's
+    // emissions are then 2^(x * log2(e) - lse * log2(e)) = softmax probabilities (same instruction count: FMUL -> FFMA)
+    float nlse = 0.f;
+    const float* lsep = nullptr;
+    if constexpr (LOGITS) lsep = p.lse + ((lane & KF) ? bsrc1 : bsrc0);
     auto load_rows = [&](auto nfc, int t0) {             // pre0[r] = (level 0, level 1) of the first utterance, ...
         constexpr int NF = decltype(nfc)::value;
         size_t o = (size_t)t0 * p.stride_t;
@@ -306,6 +312,11 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre1[r].x) : "l"(lp10 + o));
             asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre1[r].y) : "l"(lp11 + o));
             o += p.stride_t;
+        }
+        if constexpr (LOGITS) {
+            nlse = 0.f;
+            if (lane < 2 * KF && (lane & (KF - 1)) < NF)
+                asm volatile("ld.global.f32 %0, [%1];" : "=f"(nlse) : "l"(lsep + (size_t)(t0 + (lane & (KF - 1))) * p.B));
         }
     };
     auto load_chunk = [&](int j) {
@@ -320,13 +331,24 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         if (ov[1][0]) d[CPMAX + lane] = v1.x;
         if (ov[1][1]) d[CPMAX + 32 + lane] = v1.y;
     };
+    auto row_exp = [&](int r, float ns, float2& v0, float2& v1) {
+        if constexpr (LOGITS) {
+            const float n0 = __shfl_sync(FULL, ns, r), n1 = __shfl_sync(FULL, ns, KF + r);
+            v0 = make_float2(fast_exp2(fmaf(pre0[r].x, LOG2E, n0)), fast_exp2(fmaf(pre0[r].y, LOG2E, n0)));
+            v1 = make_float2(fast_exp2(fmaf(pre1[r].x, LOG2E, n1)), fast_exp2(fmaf(pre1[r].y, LOG2E, n1)));
+        } else {
+            v0 = make_float2(fast_exp(pre0[r].x), fast_exp(pre0[r].y));
+            v1 = make_float2(fast_exp(pre1[r].x), fast_exp(pre1[r].y));
+        }
+    };
     auto commit_rows = [&](auto nfc, bool kill0, bool kill1) {   // p = exp(lp) into shared memory; an idle half emits zeros
         constexpr int NF = decltype(nfc)::value;
+        const float ns = nlse * -LOG2E;
         if (kill0 || kill1) {
 #pragma unroll
             for (int r = 0; r < NF; ++r) {
-                float2 v0 = make_float2(fast_exp(pre0[r].x), fast_exp(pre0[r].y));
-                float2 v1 = make_float2(fast_exp(pre1[r].x), fast_exp(pre1[r].y));
+                float2 v0, v1;
+                row_exp(r, ns, v0, v1);
                 if (kill0) v0 = make_float2(0.f, 0.f);
                 if (kill1) v1 = make_float2(0.f, 0.f);
                 put_row(r, v0, v1);
@@ -334,8 +356,9 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         } else {
 #pragma unroll
             for (int r = 0; r < NF; ++r) {
-                put_row(r, make_float2(fast_exp(pre0[r].x), fast_exp(pre0[r].y)),
-                        make_float2(fast_exp(pre1[r].x), fast_exp(pre1[r].y)));
+                float2 v0, v1;
+                row_exp(r, ns, v0, v1);
+                put_row(r, v0, v1);
             }
         }
     };
@@ -395,7 +418,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         }
         {
             bool ok[2];
-            renorm_alpha<NSL>(a, ea, sca, lane, ok);
+            renorm_alpha<NSL>(a, ea, sca, lane, ok, p.strict_squash != 0, p.decay_max);
             if (!ok[0] && !kill0 && !flag[0]) flag[0] = 2 | (t0 << 8);
             if (!ok[1] && !kill1 && !flag[1]) flag[1] = 2 | (t0 << 8);
         }
@@ -507,18 +530,22 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         PT(10)                                          // bwd: waiting for the checkpoint
 #endif
         // a / ea hold the checkpoint of this chunk: boundary factors and the beta exponents that go with it
-        float2 scb;
+        float2 scb, scb2;
         {
-            float fb[2], sa[2], sb[2], ini[2];
+            float fb[2], fb2[2], sa[2], sb[2], sb2[2], ini[2];
             const int tend = t0 + NF;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int el = __shfl_up_sync(FULL, ea[h], 1), er = __shfl_down_sync(FULL, ea[h], 1);
                 sa[h] = lane == 0 ? 0.f : pow2i(el - ea[h]);
-                sb[h] = lane == 31 ? 0.f : pow2i(ea[h] - er);            // 2^(e_beta[l+1] - e_beta[l])
+                const int dx = max(ea[h] - er, -252);                    // 2^(e_beta[l+1] - e_beta[l]), in two factors
+                sb[h] = lane == 31 ? 0.f : pow2i(dx >> 1);
+                sb2[h] = pow2i(dx - (dx >> 1));
                 const int ebn = koff[h] - ea[h];
                 const bool starts = act[h] && tend == Tb[h];             // beta_T enters here
-                fb[h] = starts ? 0.f : pow2i(eb[h] - ebn);
+                const int df = min(max(eb[h] - ebn, -252), 252);
+                fb[h] = starts ? 0.f : pow2i(df >> 1);
+                fb2[h] = pow2i(df - (df >> 1));
                 ini[h] = starts ? pow2i(-ebn) : 0.f;
                 if (starts) {                            // beta_T = 1 must be representable in the lane that owns S-1
                     const bool owner = (S[h] - 1) / NSL == lane;
@@ -528,10 +555,11 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
             }
             sca = make_float2(sa[0], sa[1]);
             scb = make_float2(sb[0], sb[1]);
-            const float2 f2 = make_float2(fb[0], fb[1]);
+            scb2 = make_float2(sb2[0], sb2[1]);
+            const float2 f2 = make_float2(fb[0], fb[1]), f22 = make_float2(fb2[0], fb2[1]);
 #pragma unroll
             for (int jj = 0; jj < NSL; ++jj) {
-                bt[jj] = __fmul2_rn(bt[jj], f2);
+                bt[jj] = __fmul2_rn(__fmul2_rn(bt[jj], f2), f22);
                 const int s = lane * NSL + jj;
                 if (s == S[0] - 1) bt[jj].x += ini[0];
                 if (s == S[1] - 1) bt[jj].y += ini[1];
@@ -562,7 +590,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 if constexpr (REGBUF) al[q] = A[r][q];
                 else al[q] = reinterpret_cast<const float2*>(abuf + r * ARS)[q * 32 + lane];
             }
-            beta_step<NSL>(bt, ul, scb, r * RW, bl0, bl1, ep0, ep1, mb);
+            beta_step<NSL>(bt, ul, scb, scb2, r * RW, bl0, bl1, ep0, ep1, mb);
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
                 const float2 fx = __ffma2_rn(__fmul2_rn(al[q], ul[q]), zs2, magic2);
@@ -642,6 +670,20 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         bad_occ = __reduce_or_sync(FULL, bad_occ);
         if ((bad_occ & 1) && !flag[0]) flag[0] = 5;
         if ((bad_occ & 2) && !flag[1]) flag[1] = 5;
+        // The backward sweep's own total likelihood, beta_0(0) + beta_0(1), against the forward P.  Mass dropped by
+        // either sweep (alpha content squashed in a renormalisation, beta content below its tied exponent) is missing
+        // from exactly one of the two, so their ratio bounds what the occupancies can be off by.
+        {
+            const float r0 = (bt[0].x + bt[1].x) * pow2i(-ea[0]) * zi[0];
+            const float r1 = (bt[0].y + bt[1].y) * pow2i(-ea[1]) * zi[1];
+            const int disagree = (!(fabsf(r0 - 1.f) <= p.pbeta_tol) ? 1 : 0) | (!(fabsf(r1 - 1.f) <= p.pbeta_tol) ? 2 : 0);
+#ifdef MDD_PAIR_DEBUG
+            if (lane == 0) printf("PB b=%d r=%.7f flag=%d | b=%d r=%.7f flag=%d\n", bidx[0], r0, flag[0], bidx[1], r1, flag[1]);
+#endif
+            const int d0 = __shfl_sync(FULL, disagree, 0);
+            if ((d0 & 1) && act[0] && !flag[0]) flag[0] = 7;
+            if ((d0 & 2) && act[1] && !flag[1]) flag[1] = 7;
+        }
 #pragma unroll
         for (int h = 0; h < 2; ++h)
             if (act[h] && lane == 0) p.flags[bidx[h]] = flag[h];   // 0 = done here; else redone in log space
@@ -661,8 +703,8 @@ int env_int(const char* name, int dflt) {
     return e ? atoi(e) : dflt;
 }
 
-template <int NSL, bool REGBUF, int MAXR>
-int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
+template <int NSL, bool REGBUF, int MAXR, bool LOGITS>
+int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st) {
     const PairSmem lay = pair_smem_layout(NSL, REGBUF);
     size_t smem = (size_t)lay.total_floats * 4;                  // one warp (= one pair) per CTA
     const int npairs = (p.B + 1) / 2;
@@ -685,7 +727,7 @@ int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
     }
     static size_t configured = 0;
     if (configured < smem) {
-        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, REGBUF, MAXR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem) != cudaSuccess) {
             cudaGetLastError();
             return MDD_E_CUDA;
@@ -693,9 +735,15 @@ int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
         configured = smem;
     }
     const int n_ckpt = p.T / KF + 2 * KF;
-    ctc_pair_kernel<NSL, REGBUF, MAXR><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
+    ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
     MDD_CHECK_LAUNCH();
     return MDD_OK;
+}
+
+template <int NSL, bool REGBUF, int MAXR>
+int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
+    if (p.lse) return launch_cfg1<NSL, REGBUF, MAXR, true>(p, ws, st);     // lp holds logits (mdd_ctc_loss_logits)
+    return launch_cfg1<NSL, REGBUF, MAXR, false>(p, ws, st);
 }
 
 template <int NSL>
@@ -737,6 +785,12 @@ size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
 
 int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st) {
     float* w = reinterpret_cast<float*>(ws);
+    static const char* tol_env = getenv("MDD_CTC_PBETA_TOL");
+    static int strict = env_int("MDD_CTC_STRICT_SQUASH", 0);
+    p.pbeta_tol = tol_env ? (float)atof(tol_env) : 3e-5f;
+    p.strict_squash = strict;
+    static int decay = env_int("MDD_CTC_DECAY_MAX", 76 + SHIFT);
+    p.decay_max = decay;
     static int duo = env_int("MDD_CTC_DUO", 0);                  // two warps per pair (ctc_duo.cu)
     if (duo && ctc_duo_supported(p.C, p.Lmax)) return launch_ctc_duo(p, ws, st);
     switch (pick_nsl(p.Lmax)) {

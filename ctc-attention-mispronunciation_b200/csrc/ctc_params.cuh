@@ -7,6 +7,7 @@ namespace mdd {
 
 struct CtcParams {
     const float* lp;          // (T,B,C), strides (stride_t, stride_b, 1)
+    const float* lse;         // null: lp holds log-probs; else lp holds LOGITS and lse[t*B+b] their row log-sum-exp
     int T, B, C;
     int64_t stride_t, stride_b;
     const int64_t* targets;
@@ -27,6 +28,11 @@ struct CtcParams {
     int K, n_ckpt;
     int only_flagged;         // process only utterances with flags[b] != 0
     int32_t* flags;           // [B] fast path -> fallback requests
+    // pair kernel: forward/backward likelihood agreement demanded of an utterance (relative), and the earlier a-priori
+    // squash criterion (see renorm_alpha)
+    float pbeta_tol;
+    int strict_squash;
+    int decay_max;            // largest per-chunk decay (bits) of the lanes holding the bulk of alpha
 };
 
 int ctc_log_chunk(int Lmax);
@@ -45,6 +51,10 @@ bool ctc_duo_supported(int C, int Lmax);          // two warps per pair (ctc_duo
 int launch_ctc_duo(CtcParams p, void* ws, cudaStream_t st);
 size_t ctc_pair_ws_bytes(int T, int B, int Lmax);
 int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st);
+
+// per-frame log-sum-exp (+ argmax) of logits (row_lse.cu): the pre-pass of mdd_ctc_loss_logits
+int launch_row_lse(const float* x, int T, int B, int C, int64_t stride_t, int64_t stride_b, float* lse, uint8_t* amax,
+                   cudaStream_t st);
 
 // deterministic sum of nll[B] -> loss_sum (reduce.cu)
 int launch_sum_nll(const float* nll, int B, float* out, cudaStream_t st);

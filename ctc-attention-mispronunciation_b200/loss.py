@@ -28,8 +28,12 @@ def _as_len_tensor(x, dev):
 
 def ctc_loss_raw(log_probs, targets, input_lengths, target_lengths, blank=0, zero_infinity=False, want_grad=True,
                  grad_out=None, grad_scalar=1.0, algo=0, validate=True, loss_sum=None, nll=None, grad=None,
-                 status=None):
-    """One call into mdd_ctc_loss.  Returns (nll[B], grad[T,B,C] or None, status[B]); everything stays on the device."""
+                 status=None, logits=False, row_lse=None, argmax=None):
+    """One call into mdd_ctc_loss.  Returns (nll[B], grad[T,B,C] or None, status[B]); everything stays on the device.
+
+    With ``logits=True`` the first argument holds the output layer's logits and the call goes to mdd_ctc_loss_logits:
+    ``grad`` is then the gradient with respect to the logits, ``row_lse`` (T,B) fp32 receives the per-frame
+    log-sum-exp and ``argmax`` (T,B) uint8, when given, the frame arg-max."""
     L = _lib.lib()
     if log_probs.dim() == 2:
         log_probs = log_probs.unsqueeze(1)
@@ -76,11 +80,21 @@ def ctc_loss_raw(log_probs, targets, input_lengths, target_lengths, blank=0, zer
     _lib.check(L.mdd_ctc_loss_workspace_bytes(T, B, C, lmax, algo, _lib.C.byref(need)), "mdd_ctc_loss_workspace_bytes")
     ws = _rt.workspace(need.value, dev, "ctc")
     go = None if grad_out is None else grad_out.to(device=dev, dtype=torch.float32).contiguous()
-    rc = L.mdd_ctc_loss(lp.data_ptr(), T, B, C, lp.stride(0), lp.stride(1), _rt.ptr(tg), tstride, il.data_ptr(),
-                        tl.data_ptr(), lmax, blank, int(bool(zero_infinity)), _rt.ptr(go), float(grad_scalar),
-                        nll.data_ptr(), _rt.ptr(grad if want_grad else None), _rt.ptr(loss_sum), status.data_ptr(),
-                        algo, ws.data_ptr(), ws.numel(), _rt.stream_ptr(dev))
-    _lib.check(rc, "mdd_ctc_loss")
+    if logits:
+        if row_lse is None:
+            row_lse = torch.empty((T, B), dtype=torch.float32, device=dev)
+        rc = L.mdd_ctc_loss_logits(lp.data_ptr(), T, B, C, lp.stride(0), lp.stride(1), _rt.ptr(tg), tstride,
+                                   il.data_ptr(), tl.data_ptr(), lmax, blank, int(bool(zero_infinity)), _rt.ptr(go),
+                                   float(grad_scalar), nll.data_ptr(), _rt.ptr(grad if want_grad else None),
+                                   _rt.ptr(loss_sum), status.data_ptr(), row_lse.data_ptr(), _rt.ptr(argmax), algo,
+                                   ws.data_ptr(), ws.numel(), _rt.stream_ptr(dev))
+        _lib.check(rc, "mdd_ctc_loss_logits")
+    else:
+        rc = L.mdd_ctc_loss(lp.data_ptr(), T, B, C, lp.stride(0), lp.stride(1), _rt.ptr(tg), tstride, il.data_ptr(),
+                            tl.data_ptr(), lmax, blank, int(bool(zero_infinity)), _rt.ptr(go), float(grad_scalar),
+                            nll.data_ptr(), _rt.ptr(grad if want_grad else None), _rt.ptr(loss_sum),
+                            status.data_ptr(), algo, ws.data_ptr(), ws.numel(), _rt.stream_ptr(dev))
+        _lib.check(rc, "mdd_ctc_loss")
     if validate and (il_host is None or tl_host is None):
         if bool((status != 0).any()):
             raise RuntimeError("ctc_loss: input_lengths/target_lengths/targets out of range (status %s)"
@@ -99,10 +113,12 @@ def last_fallback_flags(B, dev=None):
 
 class _CTCLossFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, log_probs, targets, input_lengths, target_lengths, blank, zero_infinity, algo, validate):
+    def forward(ctx, log_probs, targets, input_lengths, target_lengths, blank, zero_infinity, algo, validate,
+                logits=False, row_lse=None, argmax=None):
         want = ctx.needs_input_grad[0]
         nll, grad, _ = ctc_loss_raw(log_probs.detach(), targets, input_lengths, target_lengths, blank, zero_infinity,
-                                    want_grad=want, algo=algo, validate=validate)
+                                    want_grad=want, algo=algo, validate=validate, logits=logits, row_lse=row_lse,
+                                    argmax=argmax)
         ctx.grad_buf = grad
         ctx.in_shape = tuple(log_probs.shape)
         ctx.in_dtype = log_probs.dtype
@@ -126,16 +142,16 @@ class _CTCLossFn(torch.autograd.Function):
         if len(ctx.in_shape) == 2:
             out = out.squeeze(1)
         out = out.to(device=ctx.in_device, dtype=ctx.in_dtype)
-        return out, None, None, None, None, None, None, None
+        return out, None, None, None, None, None, None, None, None, None, None
 
 
 def ctc_loss(log_probs, targets, input_lengths, target_lengths, blank=0, reduction="mean", zero_infinity=False,
-             algo=0, validate=True):
+             algo=0, validate=True, _logits=False, _row_lse=None, _argmax=None):
     """torch.nn.functional.ctc_loss-compatible functional form."""
     if reduction not in ("none", "mean", "sum"):
         raise ValueError("%s is not a valid value for reduction" % reduction)
     nll = _CTCLossFn.apply(log_probs, targets, input_lengths, target_lengths, int(blank), bool(zero_infinity),
-                           int(algo), bool(validate))
+                           int(algo), bool(validate), bool(_logits), _row_lse, _argmax)
     if log_probs.dim() == 2 and reduction == "none":
         nll_out = nll.squeeze(0)
     else:
@@ -170,3 +186,42 @@ class CTCLoss(torch.nn.Module):
     def forward(self, log_probs, targets, input_lengths, target_lengths):
         return ctc_loss(log_probs, targets, input_lengths, target_lengths, self.blank, self.reduction,
                         self.zero_infinity, self.algo, self.validate)
+
+
+def ctc_loss_from_logits(logits, targets, input_lengths, target_lengths, blank=0, reduction="mean",
+                         zero_infinity=False, algo=0, validate=True, row_lse=None, argmax=None):
+    """``F.ctc_loss(F.log_softmax(logits, -1), ...)`` in one step.
+
+    Replaces the tail of the reference models' forward (``out = F.log_softmax(out, dim=-1)``,
+    models/model_ctc.py:214-218, cnn_rnn.py:168-172) together with the loss call at steps/train_ctc.py:72: the
+    log-probability array is never materialised and autograd receives the gradient with respect to the logits
+    directly, (softmax - occupancy) * upstream -- the value torch reaches by back-propagating its CTC gradient through
+    log_softmax.  ``row_lse`` (T,B) fp32 / ``argmax`` (T,B) uint8, when given, are filled by the same pre-pass
+    (log_probs = logits - row_lse[..., None]; argmax feeds the train-time PER of train_ctc.py:77-81)."""
+    return ctc_loss(logits, targets, input_lengths, target_lengths, blank, reduction, zero_infinity, algo, validate,
+                    _logits=True, _row_lse=row_lse, _argmax=argmax)
+
+
+class CTCLossFromLogits(CTCLoss):
+    """CTCLoss taking the output layer's logits instead of log-probs (see ctc_loss_from_logits)."""
+
+    def forward(self, logits, targets, input_lengths, target_lengths, row_lse=None, argmax=None):
+        return ctc_loss_from_logits(logits, targets, input_lengths, target_lengths, self.blank, self.reduction,
+                                    self.zero_infinity, self.algo, self.validate, row_lse, argmax)
+
+
+def row_lse(logits, want_argmax=False):
+    """Per-frame log-sum-exp (and optionally arg-max) of (T,B,C) logits: the pre-pass of ctc_loss_from_logits."""
+    L = _lib.lib()
+    dev = _rt.device(logits)
+    x = logits.to(device=dev, dtype=torch.float32)
+    if x.dim() == 2:
+        x = x.unsqueeze(1)
+    if x.stride(2) != 1:
+        x = x.contiguous()
+    T, B, C = x.shape
+    lse = torch.empty((T, B), dtype=torch.float32, device=dev)
+    am = torch.empty((T, B), dtype=torch.uint8, device=dev) if want_argmax else None
+    _lib.check(L.mdd_row_lse(x.data_ptr(), T, B, C, x.stride(0), x.stride(1), lse.data_ptr(), _rt.ptr(am),
+                             _rt.stream_ptr(dev)), "mdd_row_lse")
+    return (lse, am) if want_argmax else lse

@@ -82,6 +82,34 @@ int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t stride_t, 
                  const float* grad_out, float grad_out_scalar, float* nll, float* grad, float* loss_sum,
                  int32_t* status, int algo, void* workspace, size_t workspace_bytes, mdd_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------------------------
+ * CTC loss + gradient straight from the output layer's LOGITS.
+ * Replaces: out = F.log_softmax(out, dim=-1)      egs/attention_aug/models/model_ctc.py:214-218,
+ *                                                 egs/cnn-rnn-ctc/models/cnn_rnn.py:168-172
+ *           followed by nn.CTCLoss / loss.backward() (call sites above) and, with `argmax`, the train-time
+ *           torch.max(out, dim=-1)                steps/train_ctc.py:77
+ *
+ * Same arguments as mdd_ctc_loss except:
+ * logits      : (T,B,C) fp32, element strides (stride_t, stride_b, 1): the input of log_softmax.
+ * grad_logits : (T,B,C) contiguous fp32 out or NULL: d(sum_b grad_out[b]*nll[b]) / d logits
+ *               = (softmax - occupancy) * grad_out[b], i.e. what autograd obtains by back-propagating torch's CTC
+ *               gradient through log_softmax (its rows sum to zero).  Rows t >= input_lengths[b] are 0.
+ * row_lse     : fp32 (T,B) out, required: log sum_c exp(logits[t,b,c]); log_probs[t,b,c] = logits[t,b,c] - row_lse[t,b].
+ * argmax      : uint8 (T,B) out or NULL: frame arg-max (first maximum wins), ready for mdd_collapse.
+ * algo        : 0, 1 or 2 (3 is not available on logits).  Workspace: mdd_ctc_loss_workspace_bytes.
+ * One pre-pass kernel streams the logits once (4*C B/frame) and writes 5 B/frame; no (T,B,C) log-prob array and no
+ * log_softmax backward pass exist.
+ * ------------------------------------------------------------------------------------------------------------------ */
+int mdd_ctc_loss_logits(const float* logits, int T, int B, int C, int64_t stride_t, int64_t stride_b,
+                        const int64_t* targets, int64_t tgt_stride, const int64_t* input_lengths,
+                        const int64_t* target_lengths, int max_target_len, int blank, int zero_infinity,
+                        const float* grad_out, float grad_out_scalar, float* nll, float* grad_logits, float* loss_sum,
+                        int32_t* status, float* row_lse, uint8_t* argmax, int algo, void* workspace,
+                        size_t workspace_bytes, mdd_stream_t stream);
+/* The pre-pass alone: row_lse (T,B) and optional argmax (T,B) of (T,B,C) logits with strides (stride_t, stride_b, 1). */
+int mdd_row_lse(const float* logits, int T, int B, int C, int64_t stride_t, int64_t stride_b, float* row_lse,
+                uint8_t* argmax, mdd_stream_t stream);
+
 /* grad[t,b,c] *= scale[b] * scalar   (autograd backward when the upstream gradient was not known in forward). */
 int mdd_ctc_scale_grad(float* grad, int T, int B, int C, const float* scale, float scalar, mdd_stream_t stream);
 

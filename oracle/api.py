@@ -72,6 +72,20 @@ def ctc_loss(lp, targets, in_len, tgt_len, blank=0, zero_infinity=False, grad_ou
     return {"nll": nll, "grad": grad, "alpha": alpha}
 
 
+def ctc_loss_logits(logits, targets, in_len, tgt_len, blank=0, zero_infinity=False, grad_out=None, dtype=np.float64):
+    """CTC loss on the output layer's logits: log_softmax (models/model_ctc.py:214-218) -> ctc_loss -> the chain rule
+    through log_softmax, g_x = g_lp - softmax * sum_c g_lp (what torch autograd computes at steps/train_ctc.py:96).
+    Returns dict(nll[B], grad[T,B,C] w.r.t. the logits, row_lse[T,B], argmax[T,B])."""
+    x = np.asarray(logits, dtype=dtype)
+    m = x.max(axis=-1, keepdims=True)
+    lse = (m + np.log(np.exp(x - m).sum(axis=-1, keepdims=True)))
+    lp = x - lse
+    r = ctc_loss(lp, targets, in_len, tgt_len, blank, zero_infinity, grad_out, dtype=dtype)
+    g = r["grad"]
+    gx = g - np.exp(lp) * g.sum(axis=-1, keepdims=True)
+    return {"nll": r["nll"], "grad": gx, "row_lse": lse[..., 0], "argmax": np.asarray(logits).argmax(axis=-1)}
+
+
 # ------------------------------------------------------------------------------------------------- greedy
 def greedy_tokens(lp, in_len, blank=0, word_id=None):
     lp = np.ascontiguousarray(lp, dtype=np.float32)

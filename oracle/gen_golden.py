@@ -7,6 +7,8 @@ fixtures next to this script.  What each file pins (reference file:line in paren
 
   assets/units, assets/lm_phone_bg.arpa   data copies of egs/attention_aug/data/{units,lm_phone_bg.arpa} (model assets)
   ctc_small.npz        torch 2.11 CPU F.ctc_loss fp32/fp64 nll+grad+alpha (call site steps/train_ctc.py:186,72,96)
+  ctc_logits_small.npz torch 2.11 CPU log_softmax -> ctc_loss -> autograd to the logits (models/model_ctc.py:214-218 +
+                       steps/train_ctc.py:72,96), fp32/fp64 nll + logit gradient + logsumexp + argmax
   greedy.npz           GreedyDecoder.decode strings (utils/ctcDecoder.py:186-200)
   beam_small.npz       BeamDecoder.decode strings / exceptions, 160 random small cases (utils/BeamSearch.py:73-153)
   beam_c4.npz          same at the C4 shape (T=500, C=43, W=10, lm_alpha 0 and 0.3), 6 utterances
@@ -86,6 +88,43 @@ def gen_ctc():
     run("c42", 60, 5, 42, 30, [60, 47, 33, 60, 31], [30, 12, 9, 1, 15])
     run("tiny", 1, 2, 5, 1, [1, 1], [1, 0])
     np.savez_compressed(os.path.join(GOLD, "ctc_small.npz"), **cases)
+
+
+def gen_ctc_logits():
+    """The reference's own tail: out = F.log_softmax(fc(x), -1) (model_ctc.py:214-218), loss = CTCLoss('sum')(out, ...),
+    loss.backward() -- gradient taken at the LOGITS."""
+    g = torch.Generator().manual_seed(4321)
+    cases = {}
+
+    def run(name, T, B, C, Lmax, in_len, tgt_len, targets=None, zero_inf=False, scale=3.0, weights=False):
+        x0 = torch.randn(T, B, C, generator=g) * scale
+        if targets is None:
+            targets = torch.randint(1, C, (B, Lmax), generator=g)
+        il, tl = torch.tensor(in_len, dtype=torch.long), torch.tensor(tgt_len, dtype=torch.long)
+        go = torch.rand(B, generator=g) + 0.5 if weights else torch.ones(B)
+        out = {"logits": x0.numpy(), "targets": targets.numpy(), "in_len": il.numpy(), "tgt_len": tl.numpy(),
+               "zero_inf": np.array(int(zero_inf)), "grad_out": go.numpy()}
+        for dt, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+            x = x0.to(dt).clone().requires_grad_(True)
+            lp = torch.log_softmax(x, -1)
+            nll = torch.nn.functional.ctc_loss(lp, targets, il, tl, blank=0, reduction="none", zero_infinity=zero_inf)
+            (nll * go.to(dt)).sum().backward()
+            out["nll_" + tag] = nll.detach().numpy()
+            out["grad_" + tag] = x.grad.numpy()
+            out["lse_" + tag] = torch.logsumexp(x.detach(), -1).numpy()
+        out["argmax"] = torch.max(x0, dim=-1)[1].numpy()
+        for k, v in out.items():
+            cases[name + "/" + k] = v
+
+    run("basic", 25, 4, 7, 6, [25, 25, 25, 25], [6, 6, 6, 6])
+    tg = torch.tensor([[3, 3, 3, 2, 2, 1], [1, 2, 3, 4, 5, 6], [0, 0, 0, 0, 0, 0], [5, 5, 1, 1, 0, 0]])
+    run("repeat_ragged", 25, 4, 7, 6, [25, 17, 9, 12], [6, 6, 0, 4], targets=tg, weights=True)
+    tg2 = torch.tensor([[2, 2, 2, 2], [1, 2, 3, 4], [4, 3, 2, 1]])
+    run("infeasible", 12, 3, 6, 4, [5, 12, 3], [4, 4, 4], targets=tg2)
+    run("infeasible_zi", 12, 3, 6, 4, [5, 12, 3], [4, 4, 4], targets=tg2, zero_inf=True)
+    run("c42", 60, 5, 42, 30, [60, 47, 33, 60, 31], [30, 12, 9, 1, 15], weights=True)
+    run("c45_wide", 40, 3, 45, 10, [40, 40, 25], [10, 4, 7], scale=12.0)
+    np.savez_compressed(os.path.join(GOLD, "ctc_logits_small.npz"), **cases)
 
 
 # ----------------------------------------------------------------------------------------------- greedy
@@ -457,10 +496,10 @@ def main():
     shutil.copy(RL.arpa_path(), os.path.join(GOLD, "assets", "lm_phone_bg.arpa"))
     vocab43 = RL.units_vocab()
     assert len(vocab43) == 43, len(vocab43)
-    steps = sys.argv[1:] or ["ctc", "greedy", "beam_small", "beam_c4", "lm", "wer", "mdd", "c1", "corpus"]
+    steps = sys.argv[1:] or ["ctc", "ctc_logits", "greedy", "beam_small", "beam_c4", "lm", "wer", "mdd", "c1", "corpus"]
     for s in steps:
         print("==", s, flush=True)
-        {"ctc": gen_ctc, "greedy": lambda: gen_greedy(vocab43), "beam_small": lambda: gen_beam_small(vocab43),
+        {"ctc": gen_ctc, "ctc_logits": gen_ctc_logits, "greedy": lambda: gen_greedy(vocab43), "beam_small": lambda: gen_beam_small(vocab43),
          "beam_c4": lambda: gen_beam_c4(vocab43), "lm": lambda: gen_lm_table(vocab43), "wer": gen_wer_corpus,
          "mdd": lambda: gen_mdd_post(vocab43), "c1": lambda: gen_c1(vocab43),
          "corpus": lambda: gen_corpus(vocab43)}[s]()

@@ -111,6 +111,244 @@ def test_ctc_config3_slice_vs_torch_cpu(M, algo):
     _check_ctc(M, lp, tg, il, tl, algo=algo, max_fallback=0)
 
 
+# ------------------------------------------------------------------------------- robustness envelope of the packed kernel
+def _aligned_logits(T, B, C, L, il, tl, tg, boost, noise, g):
+    """Posteriors of a trained model: a random valid alignment of each target (labels on even frames, blanks between)
+    gets +boost, a fraction `noise` of the frames is confidently wrong (a random class gets the boost instead)."""
+    dev = tg.device
+    x = torch.randn(T, B, C, generator=g, device=dev)
+    half = (il // 2).clamp(min=1)
+    key = torch.rand(B, T // 2, generator=g, device=dev)
+    key = key + (torch.arange(T // 2, device=dev)[None, :] >= half[:, None]) * 2.0      # positions beyond T_b/2 sort last
+    pos = key.argsort(dim=1)[:, :L].sort(dim=1)[0] * 2                                   # (B, L) label frames, increasing
+    lab = torch.zeros(B, T, dtype=torch.long, device=dev)
+    valid = torch.arange(L, device=dev)[None, :] < tl[:, None]
+    lab.scatter_(1, torch.where(valid, pos, torch.full_like(pos, T - 1)), torch.where(valid, tg, torch.zeros_like(tg)))
+    lab = lab.t().contiguous()
+    flip = torch.rand(T, B, generator=g, device=dev) < noise
+    lab = torch.where(flip, torch.randint(0, C, (T, B), generator=g, device=dev), lab)
+    x.scatter_add_(2, lab[..., None], torch.full((T, B, 1), float(boost), device=dev))
+    return x
+
+
+ENVELOPE = [  # name, boost (None = unstructured randn * scale), noise / scale, packed kernel must keep everything
+    ("randn*2", None, 2.0, True), ("randn*4", None, 4.0, False),
+    ("aligned+6", 6, 0.1, True), ("aligned+10", 10, 0.1, True), ("aligned+10 clean", 10, 0.0, True),
+    ("aligned+16", 16, 0.1, False), ("aligned+25", 25, 0.1, False), ("aligned+16 noise .3", 16, 0.3, False),
+]
+
+
+@pytest.mark.parametrize("name,boost,par,all_fast", ENVELOPE, ids=[e[0] for e in ENVELOPE])
+def test_ctc_packed_kernel_envelope(M, name, boost, par, all_fast):
+    """The packed linear-domain kernel has a finite dynamic range (block floating point, one exponent per lane and
+    chunk).  Whatever it does not hand to the log-space kernel must be RIGHT: on peaky 'trained model' posteriors, with
+    and without confidently wrong frames, every utterance it keeps agrees with the log-space kernel and a sample agrees
+    with torch CPU fp64; on the benign families it keeps all of them (no 4 ms fallback for ordinary inputs)."""
+    from mddctc.loss import ctc_loss_raw, last_fallback_flags
+    g = torch.Generator(device="cuda").manual_seed(21)
+    T, B, C, L = 600, 256, 42, 80
+    tg = torch.randint(1, C, (B, L), generator=g, device="cuda")
+    il = torch.randint(400, T + 1, (B,), generator=g, device="cuda")
+    tl = torch.randint(20, L + 1, (B,), generator=g, device="cuda")
+    if boost is None:
+        x = torch.randn(T, B, C, generator=g, device="cuda") * par
+    else:
+        x = _aligned_logits(T, B, C, L, il, tl, tg, boost, par, g)
+    lp = torch.log_softmax(x, -1)
+    n1, g1, _ = ctc_loss_raw(lp, tg, il, tl, algo=1)
+    n1, g1 = n1.clone(), g1.clone()
+    n2, g2, _ = ctc_loss_raw(lp, tg, il, tl, algo=2, validate=False)          # packed kernel alone, no fallback
+    kept = last_fallback_flags(B) == 0
+    if all_fast:
+        assert bool(kept.all()), (name, (~kept).nonzero().flatten()[:8].tolist())
+    assert float(((n1 - n2) / n1).abs()[kept].max()) < LOSS_RTOL if kept.any() else True
+    # the log-space kernel itself is good to ~2.5e-4 on high-loss inputs (fp32 log domain), hence the 4e-4
+    assert float((g1 - g2).abs().amax(dim=(0, 2))[kept].max()) < 4e-4 if kept.any() else True
+    n0, g0, _ = ctc_loss_raw(lp, tg, il, tl, algo=0)                          # the product path, against fp64
+    sel = torch.arange(0, B, B // 6)[:6]
+    ref_nll, ref_grad = _torch_cpu_ctc(lp[:, sel], tg[sel], il[sel], tl[sel], dtype=torch.float64)
+    np.testing.assert_allclose(n0[sel].cpu().numpy(), ref_nll.numpy(), rtol=LOSS_RTOL)
+    tol = GRAD_ATOL if all_fast else 4e-4
+    assert float((g0[:, sel].cpu().double() - ref_grad).abs().max()) <= tol
+
+
+# ------------------------------------------------------------------------------- CTC from logits (SURVEY 8f rank 1)
+def _torch_cpu_ctc_logits(x, tg, il, tl, zero_inf=False, dtype=torch.float32, go=None):
+    """The reference's own sequence: out = F.log_softmax(out, -1) (model_ctc.py:214-218) -> CTCLoss -> backward()."""
+    xx = x.detach().cpu().to(dtype).clone().requires_grad_(True)
+    nll = torch.nn.functional.ctc_loss(torch.log_softmax(xx, -1), tg.cpu(), il.cpu(), tl.cpu(), blank=0,
+                                       reduction="none", zero_infinity=zero_inf)
+    (nll if go is None else nll * go.to(dtype)).sum().backward()
+    return nll.detach(), xx.grad
+
+
+def _check_ctc_logits(M, x, tg, il, tl, zero_inf=False, algo=0, max_fallback=None, go=None):
+    from mddctc.loss import ctc_loss_raw, last_fallback_flags
+    T, B, C = x.shape
+    lse = torch.empty((T, B), dtype=torch.float32, device="cuda")
+    am = torch.empty((T, B), dtype=torch.uint8, device="cuda")
+    nll, grad, st = ctc_loss_raw(x.cuda(), tg.cuda(), il.cuda(), tl.cuda(), zero_infinity=zero_inf, algo=algo,
+                                 logits=True, row_lse=lse, argmax=am, grad_out=None if go is None else go.cuda())
+    if max_fallback is not None and algo == 0:
+        flags = last_fallback_flags(B)
+        assert int((flags != 0).sum()) <= max_fallback, flags.nonzero().flatten()[:8].tolist()
+    ref_nll, ref_grad = _torch_cpu_ctc_logits(x, tg, il, tl, zero_inf, go=go)
+    ref64_nll, ref64_grad = _torch_cpu_ctc_logits(x, tg, il, tl, zero_inf, torch.float64, go=go)
+    nll, grad = nll.cpu(), grad.cpu()
+    np.testing.assert_allclose(lse.cpu().numpy(), torch.logsumexp(x.double(), -1).numpy(), rtol=2e-6, atol=2e-6)
+    assert torch.equal(am.cpu().long(), torch.max(x, dim=-1)[1])
+    fin = torch.isfinite(ref_nll)
+    assert torch.equal(torch.isfinite(nll), fin)
+    assert torch.equal(nll[~fin], ref_nll[~fin])
+    np.testing.assert_allclose(nll[fin].numpy(), ref64_nll[fin].numpy(), rtol=LOSS_RTOL)
+    np.testing.assert_allclose(nll[fin].numpy(), ref_nll[fin].numpy(), rtol=LOSS_RTOL)
+    assert torch.equal(torch.isnan(grad), torch.isnan(ref_grad)), (torch.isnan(grad).sum(), torch.isnan(ref_grad).sum())
+    ok = ~torch.isnan(ref_grad)
+    dev32 = float((ref_grad[ok].double() - ref64_grad[ok]).abs().max()) if ok.any() else 0.0
+    assert float((grad[ok].double() - ref64_grad[ok]).abs().max()) <= GRAD_ATOL
+    assert float((grad[ok] - ref_grad[ok]).abs().max()) <= GRAD_ATOL + dev32
+    return nll, grad
+
+
+@pytest.mark.parametrize("algo", [1, 0])
+@pytest.mark.parametrize("name", ["basic", "repeat_ragged", "infeasible", "infeasible_zi", "c42", "c45_wide"])
+def test_ctc_logits_golden(M, name, algo):
+    z = npz("ctc_logits_small.npz")
+    g = lambda k: z[name + "/" + k]
+    from mddctc.loss import ctc_loss_raw
+    x = torch.from_numpy(g("logits")).cuda()
+    T, B, C = x.shape
+    lse = torch.empty((T, B), dtype=torch.float32, device="cuda")
+    am = torch.empty((T, B), dtype=torch.uint8, device="cuda")
+    nll, grad, st = ctc_loss_raw(x, torch.from_numpy(g("targets")).cuda(), torch.from_numpy(g("in_len")).cuda(),
+                                 torch.from_numpy(g("tgt_len")).cuda(), zero_infinity=bool(g("zero_inf")), algo=algo,
+                                 logits=True, row_lse=lse, argmax=am, grad_out=torch.from_numpy(g("grad_out")).cuda())
+    nll, grad = nll.cpu().numpy(), grad.cpu().numpy()
+    want, wg = g("nll_f32"), g("grad_f32")
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(nll), fin) and np.array_equal(nll[~fin], want[~fin])
+    np.testing.assert_allclose(nll[fin], want[fin], rtol=LOSS_RTOL)
+    np.testing.assert_allclose(nll[fin], g("nll_f64")[fin], rtol=LOSS_RTOL)
+    assert np.array_equal(np.isnan(grad), np.isnan(wg))
+    # truth = torch CPU fp64; torch's own fp32 run deviates from it on wide logits, so against fp32 the bound is 1e-4
+    # plus that deviation (as in _check_ctc)
+    dev32 = float(np.nanmax(np.abs(wg.astype(np.float64) - g("grad_f64")))) if np.isfinite(wg).any() else 0.0
+    np.testing.assert_allclose(grad, g("grad_f64"), rtol=0, atol=GRAD_ATOL, equal_nan=True)
+    np.testing.assert_allclose(grad, wg, rtol=0, atol=GRAD_ATOL + dev32, equal_nan=True)
+    np.testing.assert_allclose(lse.cpu().numpy(), g("lse_f64"), rtol=2e-6, atol=2e-6)
+    assert np.array_equal(am.cpu().numpy(), g("argmax"))
+    # and against the oracle's restatement of the same chain
+    r = O.ctc_loss_logits(g("logits"), g("targets"), g("in_len"), g("tgt_len"), zero_infinity=bool(g("zero_inf")),
+                          grad_out=g("grad_out"))
+    np.testing.assert_allclose(grad, r["grad"], rtol=0, atol=GRAD_ATOL, equal_nan=True)
+
+
+@pytest.mark.parametrize("algo", [1, 0])
+def test_ctc_logits_config2_vs_torch_cpu(M, algo):
+    """BASELINE config 2 shape on logits (scaled randn), plus the ragged / repeat / infeasible variant."""
+    g = torch.Generator().manual_seed(10)
+    x = torch.randn(200, 32, 42, generator=g) * 2.5
+    tg = torch.randint(1, 42, (32, 30), generator=g)
+    _check_ctc_logits(M, x, tg, torch.full((32,), 200), torch.full((32,), 30), algo=algo, max_fallback=0)
+    il = torch.randint(100, 201, (32,), generator=g)
+    tl = torch.randint(10, 31, (32,), generator=g)
+    tg2 = tg.clone()
+    tg2[:, 1::2] = tg2[:, 0::2]
+    il[5], tl[5] = 20, 30
+    tl[7] = 0
+    go = torch.rand(32, generator=g) + 0.5
+    _check_ctc_logits(M, x, tg2, il, tl, algo=algo, go=go)
+    _check_ctc_logits(M, x, tg2, il, tl, zero_inf=True, algo=algo)
+
+
+def test_ctc_logits_config3_slice_vs_torch_cpu(M):
+    """BASELINE config 3 shape on a B=48 slice, logits in; odd batch tail and ragged lengths."""
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(1000, 47, 42, generator=g) * 2 + torch.randn(1000, 47, 1, generator=g) * 5   # per-frame offsets
+    tg = torch.randint(1, 42, (47, 120), generator=g)
+    il = torch.full((47,), 1000)
+    tl = torch.full((47,), 120)
+    il[40:] = torch.randint(300, 1000, (7,), generator=g)
+    tl[44:] = torch.randint(1, 120, (3,), generator=g)
+    _check_ctc_logits(M, x, tg, il, tl, algo=0, max_fallback=0)
+
+
+@pytest.mark.parametrize("C", [43, 45, 5, 64])
+def test_ctc_logits_other_class_counts_and_strides(M, C):
+    g = torch.Generator().manual_seed(100 + C)
+    T, B, L = 150, 9, 20
+    big = torch.randn(T, 2 * B, C + 3, generator=g) * 1.5
+    x = big[:, ::2, :C]                                # strided view: stride_b = 2*(C+3), stride_t = 2B*(C+3)
+    tg = torch.randint(1, C, (B, L), generator=g)
+    il = torch.randint(60, T + 1, (B,), generator=g)
+    tl = torch.randint(0, L + 1, (B,), generator=g)
+    from mddctc.loss import ctc_loss_raw
+    for algo in (1, 0):
+        _check_ctc_logits(M, x.contiguous(), tg, il, tl, algo=algo, max_fallback=0)
+    # the strided view itself (no copy on the way in).  The strided pre-pass sums a row's exponentials in a different
+    # order (warp per row) than the tiled one (thread per row): equal up to the last bits of the row log-sum-exp.
+    xs = big.cuda()[:, ::2, :C]
+    a = ctc_loss_raw(xs, tg.cuda(), il.cuda(), tl.cuda(), logits=True)
+    a = (a[0].clone(), a[1].clone())
+    b = ctc_loss_raw(xs.contiguous(), tg.cuda(), il.cuda(), tl.cuda(), logits=True)
+    np.testing.assert_allclose(a[0].cpu().numpy(), b[0].cpu().numpy(), rtol=1e-6)
+    assert float((a[1] - b[1]).abs().max()) < 2e-6
+
+
+def test_ctc_from_logits_module_train_step(M):
+    """The training-step call pattern of steps/train_ctc.py:72-96 with the model tail of model_ctc.py:214-218 folded in:
+    loss = CTCLoss('sum')(logits...); loss /= batch_size; loss.backward(); plus the argmax for the train-time PER."""
+    from mddctc.loss import CTCLossFromLogits
+    g = torch.Generator().manual_seed(12)
+    T, B, C, L = 120, 6, 42, 15
+    x0 = torch.randn(T, B, C, generator=g) * 3
+    tg = torch.randint(1, C, (B, L), generator=g)
+    il = torch.tensor([120, 100, 90, 120, 61, 77])
+    tl = torch.tensor([15, 12, 9, 15, 3, 8])
+    x = x0.cuda().requires_grad_(True)
+    am = torch.empty((T, B), dtype=torch.uint8, device="cuda")
+    loss = CTCLossFromLogits(reduction="sum")(x, tg.cuda(), il.cuda(), tl.cuda(), argmax=am)
+    loss = loss / B
+    loss.backward()
+    xr = x0.clone().requires_grad_(True)
+    out = torch.log_softmax(xr, -1)
+    ref = torch.nn.CTCLoss(reduction="sum")(out, tg, il, tl) / B
+    ref.backward()
+    np.testing.assert_allclose(float(loss), float(ref), rtol=LOSS_RTOL)
+    assert float((x.grad.cpu() - xr.grad).abs().max()) <= GRAD_ATOL
+    index = torch.max(out, dim=-1)[1].transpose(0, 1)
+    assert torch.equal(am.cpu().long().transpose(0, 1), index)
+    for red in ("mean", "none"):
+        got = CTCLossFromLogits(reduction=red)(x0.cuda(), tg.cuda(), il.cuda(), tl.cuda())
+        want = torch.nn.CTCLoss(reduction=red)(out.detach(), tg, il, tl)
+        np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=LOSS_RTOL)
+
+
+def test_ctc_logits_full_config3_properties(M):
+    """Config 3 at full size (T=1000, B=4096, C=42, L=120) through size-independent properties: the logit gradient's
+    rows sum to zero, the loss equals the log-prob path's on log_softmax of the same logits, two launches agree bitwise,
+    a 16-utterance sample agrees with torch CPU."""
+    from mddctc.loss import ctc_loss_raw
+    g = torch.Generator(device="cuda").manual_seed(13)
+    T, B, C, L = 1000, 4096, 42, 120
+    x = torch.randn(T, B, C, generator=g, device="cuda") * 2
+    tg = torch.randint(1, C, (B, L), generator=g, device="cuda")
+    il = torch.full((B,), T, device="cuda")
+    tl = torch.full((B,), L, device="cuda")
+    nll, grad, _ = ctc_loss_raw(x, tg, il, tl, logits=True)
+    nll2, grad2, _ = ctc_loss_raw(x, tg, il, tl, logits=True)
+    assert torch.equal(nll, nll2) and torch.equal(grad, grad2)
+    assert float(grad.sum(-1).abs().max()) < 2e-5
+    nll_lp, grad_lp, _ = ctc_loss_raw(torch.log_softmax(x, -1), tg, il, tl)
+    np.testing.assert_allclose(nll.cpu().numpy(), nll_lp.cpu().numpy(), rtol=2e-6)
+    assert float((grad - grad_lp).abs().max()) < 2e-5
+    sel = torch.arange(0, B, B // 16)[:16]
+    ref_nll, ref_grad = _torch_cpu_ctc_logits(x[:, sel].cpu(), tg[sel].cpu(), il[sel].cpu(), tl[sel].cpu(),
+                                              dtype=torch.float64)
+    np.testing.assert_allclose(nll[sel].cpu().numpy(), ref_nll.numpy(), rtol=LOSS_RTOL)
+    assert float((grad[:, sel].cpu().double() - ref_grad).abs().max()) <= GRAD_ATOL
+
+
 @pytest.mark.parametrize("C", [43, 45, 5, 64])
 def test_ctc_other_class_counts(M, C):
     g = torch.Generator().manual_seed(C)

@@ -29,6 +29,28 @@ def test_ctc_oracle_vs_torch_golden(name):
     np.testing.assert_allclose(r32["grad"], g("grad_f32"), rtol=0, atol=2e-5, equal_nan=True)   # fp32 vs fp32 rounding
 
 
+LOGIT_CASES = ["basic", "repeat_ragged", "infeasible", "infeasible_zi", "c42", "c45_wide"]
+
+
+@pytest.mark.parametrize("name", LOGIT_CASES)
+def test_ctc_logits_oracle_vs_torch_golden(name):
+    """log_softmax -> ctc_loss -> autograd to the logits, as torch CPU computed it (gen_ctc_logits)."""
+    z = npz("ctc_logits_small.npz")
+    g = lambda k: z[name + "/" + k]
+    r = O.ctc_loss_logits(g("logits"), g("targets"), g("in_len"), g("tgt_len"), zero_infinity=bool(g("zero_inf")),
+                          grad_out=g("grad_out"))
+    np.testing.assert_allclose(r["nll"], g("nll_f64"), rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(r["grad"], g("grad_f64"), rtol=0, atol=1e-12, equal_nan=True)
+    np.testing.assert_allclose(r["row_lse"], g("lse_f64"), rtol=1e-13)
+    assert np.array_equal(r["argmax"], g("argmax"))
+    # the logit gradient of a finite utterance is (softmax - occupancy) * g: rows sum to zero, rows t >= T_b are zero
+    gr, il = r["grad"], g("in_len")
+    for b in range(gr.shape[1]):
+        if np.isfinite(gr[:, b]).all():
+            assert np.abs(gr[:, b].sum(-1)).max() < 1e-12
+            assert not gr[il[b]:, b].any()
+
+
 def test_ctc_oracle_vs_torch_live():
     g = torch.Generator().manual_seed(3)
     T, B, C, L = 40, 6, 11, 8
