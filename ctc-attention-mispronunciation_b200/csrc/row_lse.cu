@@ -9,8 +9,8 @@
 // HBM-bound stream: 4*C B read per frame.  The contiguous case walks 128-row tiles staged by the TMA engine
 // (cp.async.bulk + mbarrier, 3 stages, persistent CTAs); one thread scans one row with 8-byte shared-memory loads
 // (row stride 4*C B: with C even and C/2 odd the 16 threads of a half-warp hit 16 different 8-byte banks).
-// lse = m + log(sum exp(x - m)) with m the row maximum, libdevice expf/logf (as torch's log_softmax); argmax: first
-// maximum wins, NaN wins (torch.max).
+// lse = m + log(sum exp(x - m)) with m the row maximum (as torch's log_softmax; exponentials by MUFU.EX2, 2 ulp);
+// argmax: first maximum wins, NaN wins (torch.max).
 #include "common.cuh"
 
 namespace mdd {
@@ -19,35 +19,62 @@ namespace {
 constexpr int ROWS = 128;
 constexpr int STAGES = 3;
 
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// exact rule of torch.max for rows that hold a NaN (first NaN wins); the fast scan below ignores NaNs
+__device__ __noinline__ int row_argmax_nan(const float* r, int C) {
+    for (int c = 0; c < C; ++c)
+        if (r[c] != r[c]) return c;
+    return 0;
+}
+
+// One thread, one row.  Pass 1: the maximum (FMNMX).  Pass 2: sum of 2^((x - m) * log2 e) (FFMA + MUFU.EX2, 2 ulp) and
+// the first index that holds the maximum.  The kernel is bound by instruction issue next to HBM, hence the approximate
+// exponential: the log-sum-exp stays within 3e-7 relative of torch.logsumexp.
 template <bool VEC2>
 __device__ __forceinline__ void row_scan(const float* r, int C, float& lse, int& amax) {
-    float best = r[0];
-    int bi = 0;
+    constexpr float L2E = 1.4426950408889634f;
+    float m = -CUDART_INF_F, s = 0.f;
+    int bi = -1;
     if (VEC2) {
         const float2* r2 = reinterpret_cast<const float2*>(r);
         const int n2 = C >> 1;
+#pragma unroll 7
         for (int i = 0; i < n2; ++i) {
             const float2 v = r2[i];
-            if (v.x > best || (v.x != v.x && best == best)) { best = v.x; bi = 2 * i; }
-            if (v.y > best || (v.y != v.y && best == best)) { best = v.y; bi = 2 * i + 1; }
+            m = fmaxf(m, fmaxf(v.x, v.y));
         }
-        float s = 0.f;
+        const float nm = -m * L2E;
+#pragma unroll 7
         for (int i = 0; i < n2; ++i) {
             const float2 v = r2[i];
-            s += expf(v.x - best);
-            s += expf(v.y - best);
+            s += ex2_approx(fmaf(v.x, L2E, nm));
+            s += ex2_approx(fmaf(v.y, L2E, nm));
+            if (v.x == m && bi < 0) bi = 2 * i;
+            if (v.y == m && bi < 0) bi = 2 * i + 1;
         }
-        lse = (best == -CUDART_INF_F) ? -CUDART_INF_F : best + logf(s);
     } else {
-        for (int c = 1; c < C; ++c) {
+        for (int c = 0; c < C; ++c) m = fmaxf(m, r[c]);
+        const float nm = -m * L2E;
+        for (int c = 0; c < C; ++c) {
             const float v = r[c];
-            if (v > best || (v != v && best == best)) { best = v; bi = c; }
+            s += ex2_approx(fmaf(v, L2E, nm));
+            if (v == m && bi < 0) bi = c;
         }
-        float s = 0.f;
-        for (int c = 0; c < C; ++c) s += expf(r[c] - best);
-        lse = (best == -CUDART_INF_F) ? -CUDART_INF_F : best + logf(s);
     }
-    amax = bi;
+    if (s != s || m == CUDART_INF_F) {              // NaN in the row, or +inf (inf - inf): the slow exact path
+        float q = 0.f;
+        bool nan = false;
+        for (int c = 0; c < C; ++c) { nan |= r[c] != r[c]; q += expf(r[c] - m); }
+        s = q;
+        if (nan) bi = row_argmax_nan(r, C);
+    }
+    lse = (m == -CUDART_INF_F) ? -CUDART_INF_F : m + logf(s);
+    amax = bi < 0 ? 0 : bi;
 }
 
 // contiguous (T*B, C) rows

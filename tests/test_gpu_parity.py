@@ -292,7 +292,7 @@ def test_ctc_logits_other_class_counts_and_strides(M, C):
     a = (a[0].clone(), a[1].clone())
     b = ctc_loss_raw(xs.contiguous(), tg.cuda(), il.cuda(), tl.cuda(), logits=True)
     np.testing.assert_allclose(a[0].cpu().numpy(), b[0].cpu().numpy(), rtol=1e-6)
-    assert float((a[1] - b[1]).abs().max()) < 2e-6
+    assert float((a[1] - b[1]).abs().max()) < 1e-5
 
 
 def test_ctc_from_logits_module_train_step(M):
