@@ -9,6 +9,8 @@ fixtures next to this script.  What each file pins (reference file:line in paren
   ctc_small.npz        torch 2.11 CPU F.ctc_loss fp32/fp64 nll+grad+alpha (call site steps/train_ctc.py:186,72,96)
   ctc_logits_small.npz torch 2.11 CPU log_softmax -> ctc_loss -> autograd to the logits (models/model_ctc.py:214-218 +
                        steps/train_ctc.py:72,96), fp32/fp64 nll + logit gradient + logsumexp + argmax
+  textio.json.gz       create_input lengths + train_ctc.py:68 truncation, nosil strings / log lines of test_ctc_nosil.py,
+                       CMU -> IPA rendering of infer.py:331-333
   greedy.npz           GreedyDecoder.decode strings (utils/ctcDecoder.py:186-200)
   beam_small.npz       BeamDecoder.decode strings / exceptions, 160 random small cases (utils/BeamSearch.py:73-153)
   beam_c4.npz          same at the C4 shape (T=500, C=43, W=10, lm_alpha 0 and 0.3), 6 utterances
@@ -489,6 +491,46 @@ def gen_corpus(vocab43):
     print("corpus_mdd", total)
 
 
+def gen_textio(vocab):
+    """collate lengths (data_loader.py:151-181 + train_ctc.py:68), nosil strings and log lines
+    (test_ctc_nosil.py:196-214), CMU -> IPA table (dict/phonetic_dict.py:21-64), all from the reference's own code."""
+    create_input = RL.collate_function()
+    rng = np.random.default_rng(5)
+    batches = []
+    for _ in range(60):
+        B = int(rng.integers(1, 17))
+        flen = rng.integers(8, 1600, size=B).tolist()
+        llen = rng.integers(1, 40, size=B).tolist()
+        batch = [(torch.zeros(f, 3), torch.ones(l, dtype=torch.long), torch.ones(max(1, l // 2), dtype=torch.long), "u%d" % i)
+                 for i, (f, l) in enumerate(zip(flen, llen))]
+        _, input_sizes, _, target_sizes, _, _, _ = create_input(batch)
+        mx = max(flen)
+        outs = {}
+        for out_len in sorted({mx, mx // 4, (mx + 3) // 4, mx // 2, 1 + mx // 8}):
+            if out_len > 0:
+                outs[str(out_len)] = (input_sizes * out_len).long().tolist()          # train_ctc.py:68
+        batches.append({"feature_lengths": flen, "label_lengths": llen, "input_sizes_f32": [float(v) for v in input_sizes],
+                        "target_sizes": target_sizes.tolist(), "frame_lengths": outs})
+    run = RL.nosil_log_loops()
+    units = [vocab[i] for i in sorted(vocab) if i >= 2]
+    logs = []
+    for k in range(12):
+        n = int(rng.integers(1, 6))
+        def seq():
+            toks = [("sil" if rng.random() < 0.25 else units[int(rng.integers(len(units)))]) for _ in range(int(rng.integers(0, 12)))]
+            return " ".join(toks)
+        decoded = [(" " + seq()) if rng.random() < 0.5 else seq() for _ in range(n)]     # greedy strings lead with a blank
+        labels, canon = [seq() for _ in range(n)], [seq() for _ in range(n)]
+        utts = ["spk%d_utt%03d" % (k, i) for i in range(n)]
+        d, l, c, t1, t2, t3 = run(decoded, labels, canon, utts)
+        logs.append({"decoded": decoded, "labels": labels, "canonicals": canon, "utt_list": utts, "decoded_nosil": d,
+                     "labels_nosil": l, "canonicals_nosil": c, "decode_seq": t1, "human_seq": t2, "transcribe": t3})
+    table = RL.cmu_ipa_table()
+    probe = sorted(set(list(table) + [k.lower() for k in table] + units + ["sil", "err", "UNK", "xx"]))
+    ipa = {c: table.get(c.upper(), c) for c in probe}                                     # infer.py:331-333
+    jdump("textio.json.gz", {"batches": batches, "logs": logs, "ipa": ipa})
+
+
 def main():
     assert RL.available(), "reference tree not mounted"
     os.makedirs(os.path.join(GOLD, "assets"), exist_ok=True)
@@ -496,13 +538,13 @@ def main():
     shutil.copy(RL.arpa_path(), os.path.join(GOLD, "assets", "lm_phone_bg.arpa"))
     vocab43 = RL.units_vocab()
     assert len(vocab43) == 43, len(vocab43)
-    steps = sys.argv[1:] or ["ctc", "ctc_logits", "greedy", "beam_small", "beam_c4", "lm", "wer", "mdd", "c1", "corpus"]
+    steps = sys.argv[1:] or ["ctc", "ctc_logits", "greedy", "beam_small", "beam_c4", "lm", "wer", "mdd", "c1", "corpus", "textio"]
     for s in steps:
         print("==", s, flush=True)
         {"ctc": gen_ctc, "ctc_logits": gen_ctc_logits, "greedy": lambda: gen_greedy(vocab43), "beam_small": lambda: gen_beam_small(vocab43),
          "beam_c4": lambda: gen_beam_c4(vocab43), "lm": lambda: gen_lm_table(vocab43), "wer": gen_wer_corpus,
          "mdd": lambda: gen_mdd_post(vocab43), "c1": lambda: gen_c1(vocab43),
-         "corpus": lambda: gen_corpus(vocab43)}[s]()
+         "corpus": lambda: gen_corpus(vocab43), "textio": lambda: gen_textio(vocab43)}[s]()
 
 
 if __name__ == "__main__":

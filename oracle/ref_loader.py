@@ -110,6 +110,55 @@ def corpus_eval_functions():
     return _cache["corpus"]
 
 
+def collate_function(eg="attention_aug"):
+    """utils/data_loader.py::create_input (:151-181), AST-extracted (the module itself needs kaldiio)."""
+    src = open(os.path.join(eg_dir(eg), "utils", "data_loader.py")).read()
+    tree = ast.parse(src)
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "create_input"]
+    import torch
+    ns = {"torch": torch}
+    exec(compile(ast.Module(body=body, type_ignores=[]), "data_loader.py", "exec"), ns)
+    return ns["create_input"]
+
+
+def cmu_ipa_table(eg="attention_aug"):
+    """The dict literal assigned to self.cmu_to_ipa_wiki in dict/phonetic_dict.py:21-64 (the module needs ECDICT)."""
+    src = open(os.path.join(eg_dir(eg), "dict", "phonetic_dict.py")).read()
+    for n in ast.walk(ast.parse(src)):
+        if isinstance(n, ast.Assign) and isinstance(n.value, ast.Dict) and "cmu_to_ipa_wiki" in ast.dump(n.targets[0]):
+            return ast.literal_eval(n.value)
+    raise RuntimeError("cmu_to_ipa_wiki not found")
+
+
+def nosil_log_loops(eg="attention_aug"):
+    """The two loops of steps/test_ctc_nosil.py::test that build the *_nosil strings (:196-209) and write the three
+    logs (:211-214), AST-extracted; returns run(decoded, labels, canonicals, utt_list) -> (decoded_nosil, labels_nosil,
+    canonicals_nosil, decode_seq text, human_seq text, transcribe text)."""
+    import io
+    src = open(os.path.join(eg_dir(eg), "steps", "test_ctc_nosil.py")).read()
+    test_fn = [n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == "test"][0]
+    loops = []
+    for n in ast.walk(test_fn):
+        if isinstance(n, ast.For) and isinstance(n.target, ast.Name):
+            d = ast.dump(n)
+            if n.target.id == "i" and "ref_precess" in d and "labels_nosil" in d:
+                loops.append((n.lineno, n))
+            if n.target.id == "x" and "w3" in d and "w1" in d and "wer" not in d:
+                loops.append((n.lineno, n))
+    loops = [n for _, n in sorted(loops, key=lambda t: t[0])]
+    assert len(loops) == 2, len(loops)
+    code = compile(ast.Module(body=loops, type_ignores=[]), "test_ctc_nosil.py", "exec")
+
+    def run(decoded, labels, canonicals, utt_list):
+        w1, w2, w3 = io.StringIO(), io.StringIO(), io.StringIO()
+        ns = {"decoded": list(decoded), "labels": list(labels), "canonicals": list(canonicals), "utt_list": list(utt_list),
+              "targets": list(labels), "decoded_nosil": [], "labels_nosil": [], "canonicals_nosil": [],
+              "w1": w1, "w2": w2, "w3": w3}
+        exec(code, ns)
+        return ns["decoded_nosil"], ns["labels_nosil"], ns["canonicals_nosil"], w1.getvalue(), w2.getvalue(), w3.getvalue()
+    return run
+
+
 def units_vocab(eg="attention_aug"):
     """int2char as data_loader.Vocab builds it (data_loader.py:13-52): 0 'blank', 1 'UNK', then data/units order."""
     int2char = {0: "blank", 1: "UNK"}

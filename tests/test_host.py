@@ -148,3 +148,67 @@ def test_sharded_loss_gloo_world2(tmp_path):
                               stderr=subprocess.STDOUT, text=True) for r in range(2)]
     outs = [p.communicate(timeout=240)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
+
+
+# ------------------------------------------------------------------------------- SURVEY 8f ranks 3 and 4 (host glue)
+def test_collate_lengths_match_reference_create_input():
+    """data_loader.py:151-181 + train_ctc.py:68, recorded from the reference's own create_input (gen_textio): the
+    fractional float32 detour and its truncation are reproduced bit for bit, including the one-frame-short cases."""
+    import torch
+    from conftest import jload
+    from mddctc import textio
+    G = jload("textio.json.gz")
+    short = total = 0
+    for b in G["batches"]:
+        frac = textio.fractional_input_sizes(b["feature_lengths"])
+        assert frac.dtype == torch.float32
+        assert [float(v) for v in frac] == b["input_sizes_f32"]
+        for out_len, want in b["frame_lengths"].items():
+            got = textio.frame_lengths(frac, int(out_len))
+            assert got.dtype == torch.int64 and got.tolist() == want
+            exact = textio.exact_frame_lengths(b["feature_lengths"], int(out_len)).tolist()
+            assert all(e - 1 <= g <= e for g, e in zip(want, exact))
+            short += sum(g != e for g, e in zip(want, exact))
+            total += len(want)
+        il, tl = textio.collate_lengths(b["feature_lengths"], b["label_lengths"], max(b["feature_lengths"]) // 4 or 1)
+        assert tl.tolist() == b["target_sizes"] and il.dtype == torch.int64
+    assert 0 < short < 0.1 * total          # the off-by-one really occurs (SURVEY App. C: a few percent)
+
+
+def test_eval_log_formats_match_reference(tmp_path):
+    """test_ctc_nosil.py:196-214 executed by gen_textio: nosil strings and the three log files, byte for byte."""
+    from conftest import jload
+    from mddctc import textio
+    G = jload("textio.json.gz")
+    with textio.EvalLogs(str(tmp_path)) as logs:
+        for c in G["logs"]:
+            d, l, k = logs.write_batch(c["utt_list"], c["decoded"], c["labels"], c["canonicals"])
+            assert d == c["decoded_nosil"] and l == c["labels_nosil"] and k == c["canonicals_nosil"]
+            assert "".join(textio.seq_log_lines(c["utt_list"], d)) == c["decode_seq"]
+    for key, name in textio.EvalLogs.NAMES.items():
+        want = "".join(c[{"decoded": "decode_seq", "labels": "human_seq", "canonicals": "transcribe"}[key]] for c in G["logs"])
+        assert open(tmp_path / name).read() == want
+    assert textio.ids_to_string([3, 1, 2, 0, 0], 3, {0: "blank", 1: "a", 2: "b", 3: "c"}) == "c a b"
+    assert textio.phone_list(" aa  b sil ") == ["aa", "b", "sil"]
+
+
+def test_cmu_to_ipa_matches_reference_table():
+    from conftest import jload
+    from mddctc import textio
+    ipa = jload("textio.json.gz")["ipa"]
+    keys = sorted(ipa)
+    assert textio.cmu_to_ipa(keys) == [ipa[k] for k in keys]
+    assert len(textio.CMU_TO_IPA) == 41 and textio.IPA_TO_CMU["ə"] == "AH0"
+
+
+def test_bucketed_batches_cover_and_bound_waste():
+    import numpy as np
+    from mddctc import textio
+    rng = np.random.default_rng(0)
+    lens = rng.integers(50, 1501, size=1000).tolist()
+    batches = textio.bucketed_batches(lens, batch_size=32, width=64)
+    assert sorted(i for b in batches for i in b) == list(range(1000))
+    assert all(len(b) <= 32 for b in batches)
+    assert all(max(lens[i] for i in b) - min(lens[i] for i in b) < 64 for b in batches)
+    again = textio.bucketed_batches(lens, batch_size=32, width=64, shuffle_seed=3)
+    assert sorted(map(tuple, again)) == sorted(map(tuple, batches)) and again != batches
