@@ -32,13 +32,14 @@ int ctc_kernel_choice(int C, int Lmax, int algo) {
     return 0;
 }
 struct CtcWs {
-    size_t off_offsets, off_flags, off_ckpt, off_fast, total;
+    size_t off_offsets, off_flags, off_list, off_ckpt, off_fast, total;
 };
 CtcWs ctc_ws_layout(int T, int B, int C, int Lmax, int algo) {
     CtcWs w{};
     size_t o = 0;
     w.off_offsets = o; o = align_up(o + (size_t)B * 8, 256);
     w.off_flags = o;   o = align_up(o + (size_t)B * 4, 256);
+    w.off_list = o;    o = align_up(o + (size_t)(B + 1) * 4, 256);     // second tier: flagged utterances + their count
     w.off_ckpt = o;
     const int kern = ctc_kernel_choice(C, Lmax, algo);           // 0 log-space only, 1 pair kernel, 2 scalar kernel
     if (algo != 2) o = align_up(o + ctc_log_ckpt_bytes(T, B, Lmax), 256);
@@ -85,6 +86,10 @@ int ctc_loss_impl(const float* log_probs, int T, int B, int C, int64_t stride_t,
     p.tgt_offsets = reinterpret_cast<const int64_t*>(ws + w.off_offsets);
     p.flags = reinterpret_cast<int32_t*>(ws + w.off_flags);
     p.ckpt = reinterpret_cast<float*>(ws + w.off_ckpt);
+    if (algo == 0) {                                             // the packed kernel's second tier (ctc_pair.cu)
+        p.list = reinterpret_cast<int32_t*>(ws + w.off_list);
+        p.list_count = p.list + B;
+    }
     int rc;
     if (tgt_stride == 0) {
         rc = launch_tgt_offsets(target_lengths, B, reinterpret_cast<int64_t*>(ws + w.off_offsets), st);

@@ -29,6 +29,7 @@
 //    by cp.async, log-prob rows are prefetched into L2 two chunks ahead of their register loads.
 //  * Anything unusual (infeasible, empty, malformed, over/underflow) sets flags[b]; ctc_log.cu redoes exactly those
 //    utterances in the same stream with torch's inf / NaN / zero_infinity semantics.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <type_traits>
@@ -67,15 +68,18 @@ __host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf) {
     return s;
 }
 
-template <int NSL, bool REGBUF, int MAXR, bool LOGITS>
-__global__ void __maxnreg__(MAXR)
-ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
+// CH = frames per chunk (renormalisation / checkpoint period): 8 for the first pass over the whole batch, 2 for the
+// second tier, which (LIST) walks the compacted list of the utterances the first pass flagged: four times the dynamic
+// range per frame for about twice the time per frame, in front of the log-space kernel.
+// One pair of utterances, start to finish.  `pair` selects the utterances (2*pair, 2*pair+1 of the batch, or of the
+// compacted list), `slot` the checkpoint block of the workspace this warp may use.
+template <int NSL, bool REGBUF, bool LOGITS, int CH, bool LIST>
+__device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restrict__ ckpt_ws, int n_ckpt, int pair,
+                                              int slot, int n_utt) {
     using G = PGeo<NSL>;
     constexpr int NL = G::NL, ARS = G::ARS, CKW = G::CKW;
+    static_assert(CH >= 1 && CH <= KF && (CH & (CH - 1)) == 0, "chunk length: a power of two up to the staged rows");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int pair = blockIdx.x * (blockDim.x >> 5) + warp;
-    const int npairs = (p.B + 1) >> 1;
-    if (pair >= npairs) return;
 
     extern __shared__ __align__(16) float smem_f[];
     const PairSmem lay = pair_smem_layout(NSL, REGBUF);
@@ -98,9 +102,10 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     static_assert(2 * KF * RW >= 1280 + 288 + 128, "setup scratch must fit in the occupancy + emission rows");
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-        const int b = 2 * pair + h;
+        const bool have = 2 * pair + h < n_utt;
+        const int b = LIST ? (have ? p.list[2 * pair + h] : p.list[2 * pair]) : 2 * pair + h;
         bidx[h] = b;
-        act[h] = b < p.B;
+        act[h] = have;
         Tb[h] = 0; L[h] = 0;
         if (act[h]) {
             const long long Tb64 = p.in_len[b], L64 = p.tgt_len[b];
@@ -269,14 +274,14 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     // Chunks are either full (KF frames) or single frames (the remainders of the two phases), so that every chunk
     // body is straight-line code: joint phase [0, Tmin), then the longer utterance alone [Tmin, Tmax).
     const int Tmin = min(Tb[0], Tb[1]), Tmax = max(Tb[0], Tb[1]);
-    const int nJ8 = Tmin / KF, cJ = nJ8 + Tmin % KF;
-    const int nS8 = (Tmax - Tmin) / KF, cS = cJ + nS8;
-    const int nch = cS + (Tmax - Tmin) % KF;
+    const int nJ8 = Tmin / CH, cJ = nJ8 + Tmin % CH;
+    const int nS8 = (Tmax - Tmin) / CH, cS = cJ + nS8;
+    const int nch = cS + (Tmax - Tmin) % CH;
     auto chunk_geom = [&](int j, int& t0) -> bool {               // true: full chunk
-        if (j < nJ8) { t0 = j * KF; return true; }
-        if (j < cJ) { t0 = nJ8 * KF + (j - nJ8); return false; }
-        if (j < cS) { t0 = Tmin + (j - cJ) * KF; return true; }
-        t0 = Tmin + nS8 * KF + (j - cS);
+        if (j < nJ8) { t0 = j * CH; return true; }
+        if (j < cJ) { t0 = nJ8 * CH + (j - nJ8); return false; }
+        if (j < cS) { t0 = Tmin + (j - cJ) * CH; return true; }
+        t0 = Tmin + nS8 * CH + (j - cS);
         return false;
     };
     // rows are always read from a live utterance's memory; an idle half re-reads its partner's rows
@@ -294,7 +299,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
 #pragma unroll
     for (int h = 0; h < 2; ++h) g[h] = act[h] ? (p.grad_out ? p.grad_out[bidx[h]] : 1.f) * p.gscalar : 0.f;
 
-    float2 pre0[KF], pre1[KF];                          // the next chunk's rows, in flight
+    float2 pre0[CH], pre1[CH];                          // the next chunk's rows, in flight
     // LOGITS: lane r holds -lse * log2(e) of row r of the first utterance, lane KF + r of the second; the row's
     // emissions are then 2^(x * log2(e) - lse * log2(e)) = softmax probabilities (same instruction count: FMUL -> FFMA)
     float nlse = 0.f;
@@ -321,7 +326,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     };
     auto load_chunk = [&](int j) {
         int t0;
-        if (chunk_geom(j, t0)) load_rows(IC<KF>{}, t0);
+        if (chunk_geom(j, t0)) load_rows(IC<CH>{}, t0);
         else load_rows(IC<1>{}, t0);
     };
     auto put_row = [&](int r, float2 v0, float2 v1) {
@@ -373,7 +378,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     int flag[2] = {0, 0};
     float zi[2] = {0.f, 0.f}, zc[2] = {0.f, 0.f};
     int koff[2] = {0, 0};
-    float* ck = ckpt_ws + (size_t)pair * n_ckpt * CKW;
+    float* ck = ckpt_ws + (size_t)slot * n_ckpt * CKW;
 
     PT_DECL
     PT(0)                                               // setup
@@ -404,13 +409,13 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         __syncwarp();
         PT(8)                                           // fwd: commit
         if (j + 1 < nch) load_chunk(j + 1);
-        if constexpr (NF == KF) {                       // rows two chunks ahead -> L2 (the next chunk's are in flight)
+        if constexpr (NF == CH) {                       // rows two chunks ahead -> L2 (the next chunk's are in flight)
 #pragma unroll
             for (int k = 0; k < 2; ++k) {
                 const int idx = lane + 32 * k;          // 48 tasks: row, utterance, 128-byte part of its 4*C bytes
                 const int r = idx / 6, u = (idx % 6) / 3, part = idx % 3;
-                const int t = t0 + 2 * KF + r;
-                if (idx < 6 * KF && t < Tmax) {
+                const int t = t0 + 2 * CH + r;
+                if (idx < 6 * CH && t < Tmax) {
                     const float* q = (u ? lpb1 : lpb0) + (size_t)t * p.stride_t + min(part * 32, C - 1);
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
                 }
@@ -468,7 +473,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     };
     for (int j = 0; j < nch; ++j) {
         int t0;
-        if (chunk_geom(j, t0)) fwd_chunk(IC<KF>{}, j, t0);
+        if (chunk_geom(j, t0)) fwd_chunk(IC<CH>{}, j, t0);
         else fwd_chunk(IC<1>{}, j, t0);
     }
     if (!want_grad || ((flag[0] || !act[0]) && (flag[1] || !act[1]))) {
@@ -605,7 +610,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
                 for (int k = 0; k < 2; ++k) {
                     const int idx = lane + 32 * k;      // 48 tasks: row, utterance, 128-byte part of its 4*C bytes
                     const int r = idx / 6, u = (idx % 6) / 3, part = idx % 3;
-                    if (idx < 6 * KF) {
+                    if (idx < 6 * CH) {
                         const float* q = (u ? lpb1 : lpb0) + (size_t)(tq + r) * p.stride_t + min(part * 32, C - 1);
                         asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
                     }
@@ -657,7 +662,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     ckpt_issue(nch - 1);
     for (int j = nch - 1; j >= 0; --j) {
         int t0;
-        if (chunk_geom(j, t0)) bwd_chunk(IC<KF>{}, j, t0);
+        if (chunk_geom(j, t0)) bwd_chunk(IC<CH>{}, j, t0);
         else bwd_chunk(IC<1>{}, j, t0);
     }
     PT_FLUSH
@@ -690,6 +695,23 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     }
 }
 
+template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST>
+__global__ void __maxnreg__(MAXR)
+ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
+    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if constexpr (!LIST) {
+        if (w < ((p.B + 1) >> 1)) ctc_pair_body<NSL, REGBUF, LOGITS, CH, false>(p, ckpt_ws, n_ckpt, w, w, p.B);
+    } else {
+        // second tier: this warp owns checkpoint block w and walks the pairs w, w + #warps, ... of the flagged list
+        const int n_utt = *p.list_count, stride = gridDim.x * (blockDim.x >> 5);
+        for (int pr = w; 2 * pr < n_utt; pr += stride) {
+            ctc_pair_body<NSL, REGBUF, LOGITS, CH, true>(p, ckpt_ws, n_ckpt, pr, w, n_utt);
+            asm volatile("cp.async.wait_all;" ::: "memory");
+            __syncwarp();
+        }
+    }
+}
+
 int pick_nsl(int Lmax) {
     if (Lmax <= PGeo<2>::LCAP) return 2;
     if (Lmax <= PGeo<4>::LCAP) return 4;
@@ -703,11 +725,38 @@ int env_int(const char* name, int dflt) {
     return e ? atoi(e) : dflt;
 }
 
-template <int NSL, bool REGBUF, int MAXR, bool LOGITS>
-int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st) {
+// ordered compaction of the flagged utterances: list[0..count) = { b : flags[b] != 0 }, ascending (one CTA)
+__global__ void __launch_bounds__(1024) compact_flagged_kernel(const int32_t* __restrict__ flags, int B,
+                                                               int32_t* __restrict__ list, int32_t* __restrict__ count) {
+    __shared__ int wsum[32];
+    __shared__ int base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) base = 0;
+    __syncthreads();
+    for (int b0 = 0; b0 < B; b0 += 1024) {
+        const int b = b0 + tid;
+        const bool f = b < B && flags[b] != 0;
+        const unsigned m = __ballot_sync(0xffffffffu, f);
+        if (lane == 0) wsum[warp] = __popc(m);
+        __syncthreads();
+        int off = base;
+        for (int w = 0; w < warp; ++w) off += wsum[w];
+        if (f) list[off + __popc(m & ((1u << lane) - 1))] = b;
+        __syncthreads();
+        if (tid == 0) {
+            int t = 0;
+            for (int w = 0; w < 32; ++w) t += wsum[w];
+            base += t;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) *count = base;
+}
+
+template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST>
+int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st, int npairs) {
     const PairSmem lay = pair_smem_layout(NSL, REGBUF);
     size_t smem = (size_t)lay.total_floats * 4;                  // one warp (= one pair) per CTA
-    const int npairs = (p.B + 1) / 2;
     // Warps per SM: the register file allows 8; fewer when that packs the pairs into full waves (a pair runs for the
     // whole kernel, so 13.8 pairs per SM are better served by 7 warps x 2 waves than by 8 + 5.8).
     static int wps_env = env_int("MDD_CTC_PAIR_WPS", 0);
@@ -727,23 +776,41 @@ int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st) {
     }
     static size_t configured = 0;
     if (configured < smem) {
-        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem) != cudaSuccess) {
             cudaGetLastError();
             return MDD_E_CUDA;
         }
         configured = smem;
     }
-    const int n_ckpt = p.T / KF + 2 * KF;
-    ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
+    const int n_ckpt = p.T / CH + 2 * CH;
+    ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
     MDD_CHECK_LAUNCH();
     return MDD_OK;
 }
 
+constexpr int CH2 = 2;                                           // chunk length of the second tier
+
+template <int NSL, bool REGBUF, int MAXR, bool LOGITS>
+int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
+    const int npairs = (p.B + 1) / 2;
+    int rc = launch_cfg1<NSL, REGBUF, MAXR, LOGITS, KF, false>(p, ws, st, npairs);
+    if (rc || !p.list) return rc;
+    // second tier: the flagged utterances again, renormalised every CH2 frames, in the same checkpoint workspace
+    const size_t ws_floats = (size_t)npairs * (p.T / KF + 2 * KF) * PGeo<NSL>::CKW;
+    const size_t per_pair = (size_t)(p.T / CH2 + 2 * CH2) * PGeo<NSL>::CKW;
+    const int cap = (int)std::min<size_t>(ws_floats / per_pair, (size_t)npairs);
+    if (cap <= 0) return MDD_OK;
+    compact_flagged_kernel<<<1, 1024, 0, st>>>(p.flags, p.B, p.list, p.list_count);
+    MDD_CHECK_LAUNCH();
+    p.list_cap_pairs = cap;
+    return launch_cfg1<NSL, REGBUF, MAXR, LOGITS, CH2, true>(p, ws, st, cap);
+}
+
 template <int NSL, bool REGBUF, int MAXR>
 int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
-    if (p.lse) return launch_cfg1<NSL, REGBUF, MAXR, true>(p, ws, st);     // lp holds logits (mdd_ctc_loss_logits)
-    return launch_cfg1<NSL, REGBUF, MAXR, false>(p, ws, st);
+    if (p.lse) return launch_tiers<NSL, REGBUF, MAXR, true>(p, ws, st);    // lp holds logits (mdd_ctc_loss_logits)
+    return launch_tiers<NSL, REGBUF, MAXR, false>(p, ws, st);
 }
 
 template <int NSL>

@@ -32,6 +32,10 @@ struct CtcParams {
     // squash criterion (see renorm_alpha)
     float pbeta_tol;
     int strict_squash;
+    // second tier of the pair kernel: compacted list of the utterances the first pass flagged (null: no second tier)
+    int32_t* list;
+    int32_t* list_count;
+    int list_cap_pairs;
     int decay_max;            // largest per-chunk decay (bits) of the lanes holding the bulk of alpha
 };
 

@@ -29,6 +29,12 @@ def run(name, x, tg, il, tl):
     e0.record()
     for _ in range(5): ctc_loss_raw(lp,tg,il,tl,algo=0,validate=False)
     e1.record(); torch.cuda.synchronize()
+    n0,g0,_ = ctc_loss_raw(lp,tg,il,tl,algo=0,validate=False)
+    torch.cuda.synchronize()
+    fl0 = last_fallback_flags(B)
+    fin = torch.isfinite(n1)
+    print('      algo0: left for the log kernel %d | all utterances vs log kernel: grad %.2e nll rel %.2e' % (
+        int((fl0 != 0).sum()), float((g0-g1).abs().amax(dim=(0,2))[fin].max()), float(((n0-n1)/n1).abs()[fin].max())))
     print('%-22s B=%d flagged %s | unflagged: max grad diff vs log kernel %.2e, nll rel %.2e | ms algo0 %.3f nll %.0f inf %d' % (
         name, B, dict(cnt), float(gd[ok].max()) if ok.any() else -1, float(nrel[ok].max()) if ok.any() else -1,
         e0.elapsed_time(e1)/5, float(n1[torch.isfinite(n1)].mean()), int((~torch.isfinite(n1)).sum())), flush=True)
