@@ -27,8 +27,19 @@
 //    that owns the position reads it back.  Integer addition is associative: results are bitwise reproducible.
 //  * Loads that travel far never sit on a register scoreboard next to the lattice's LDS traffic: checkpoints come back
 //    by cp.async, log-prob rows are prefetched into L2 two chunks ahead of their register loads.
-//  * Anything unusual (infeasible, empty, malformed, over/underflow) sets flags[b]; ctc_log.cu redoes exactly those
-//    utterances in the same stream with torch's inf / NaN / zero_infinity semantics.
+//  * Dynamic range.  One exponent per lane and chunk is a finite window, and peaky posteriors move 20-35 bits per
+//    frame.  A renormalised lane keeps its maximum at 2^SHIFT; a lane far below its left neighbour is pulled up to
+//    2^-GAP of it and may lose its own content, which the backward sweep does not share: its total likelihood
+//    beta_0(0) + beta_0(1) must agree with the forward P (flag 7).  What that check cannot see (beta's exponents are
+//    tied to alpha's, so beta is blind to what a lane lost once the lane's exponent followed the loss down) is
+//    excluded in the forward sweep: the lanes holding the bulk of the mass must not decay by more than 2^decay_max
+//    inside one chunk (flag 2).  DESIGN.md 5.1 has the measured envelope.
+//  * Three tiers.  Anything unusual (infeasible, empty, malformed, over/underflow, the guards above) sets flags[b].
+//    The flagged utterances are compacted into a list and run again by this same kernel at CH = 2 frames per chunk
+//    (LIST instantiation, persistent warps over the first pass's checkpoint blocks); ctc_log.cu then redoes whatever
+//    is still flagged in the same stream with torch's inf / NaN / zero_infinity semantics.
+//  * LOGITS instantiation: lp holds the output layer's logits, lse their row log-sum-exp (row_lse.cu); the emission
+//    is 2^(x log2 e - lse log2 e) and the gradient written is the one with respect to the logits.
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
