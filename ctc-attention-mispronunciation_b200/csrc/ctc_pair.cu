@@ -827,13 +827,17 @@ int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
 template <int NSL>
 int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
     if constexpr (NSL == 8) {
-        static int regbuf = env_int("MDD_CTC_PAIR_REGBUF", 1), maxr = env_int("MDD_CTC_PAIR_MAXR", 255);
+#ifdef MDD_PAIR_EXPERIMENTS                                      // A/B builds only (scratch/variants.sh): alpha label states
+        static int regbuf = env_int("MDD_CTC_PAIR_REGBUF", 1), maxr = env_int("MDD_CTC_PAIR_MAXR", 255);   // in shared memory,
+        if (!regbuf) {                                           // optionally with a register cap
+            if (maxr >= 255) return launch_cfg<NSL, false, 255>(p, ws, st);
+            return launch_cfg<NSL, false, 168>(p, ws, st);
+        }
+#endif
 #ifndef MDD_PAIR_MAXR
 #define MDD_PAIR_MAXR 255
 #endif
-        if (regbuf) return launch_cfg<NSL, true, MDD_PAIR_MAXR>(p, ws, st);
-        if (maxr >= 255) return launch_cfg<NSL, false, 255>(p, ws, st);
-        return launch_cfg<NSL, false, 168>(p, ws, st);
+        return launch_cfg<NSL, true, MDD_PAIR_MAXR>(p, ws, st);
     }
     if constexpr (NSL < 8) return launch_cfg<NSL, true, 255>(p, ws, st);
     return launch_cfg<NSL, false, 255>(p, ws, st);               // NSL = 16: the alpha buffer does not fit in registers
