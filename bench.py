@@ -280,7 +280,7 @@ def run_ours(args):
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": ncu_traffic(name, args.algo), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                              "kernel_ms": kernel_ms,
-                             "note": "CUDA-event time of one mdd_ctc_loss call (main kernel + fallback sweep + loss sum)"},
+                             "note": "CUDA-event time of one mdd_ctc_loss call (first packed pass + compaction and second tier of the flagged utterances + log-space sweep, both empty here + loss sum)"},
                 "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                         "ms_per_step": float(e2e_ms)},
                 "gpu_launches": launches, "wall_s_timed_region": t_wall}

@@ -104,7 +104,9 @@ def ctc_loss_raw(log_probs, targets, input_lengths, target_lengths, blank=0, zer
 
 def last_fallback_flags(B, dev=None):
     """Diagnostics: the per-utterance flags the last mdd_ctc_loss call on this device left in its workspace
-    (0 = the packed linear-domain kernel produced the result, otherwise the log-space kernel redid the utterance)."""
+    (0 = the packed linear-domain kernel produced the result -- in its first pass or, with algo=0, in its second tier at
+    2 frames per chunk -- otherwise the log-space kernel redid the utterance; after an algo=2 call: what the first pass
+    alone handed on)."""
     dev = _rt.device() if dev is None else dev
     ws = _rt._ws_cache[(dev.index, "ctc")]
     off = (B * 8 + 255) // 256 * 256

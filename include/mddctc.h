@@ -71,8 +71,9 @@ void mdd_launch_count_reset(void);
  * grad      : (T,B,C) contiguous fp32 out, or NULL for loss only.  Rows t >= input_lengths[b] are written as 0.
  * loss_sum  : optional fp32 scalar out = sum_b nll[b] (deterministic fixed-order tree), e.g. an NCCL send buffer.
  * status    : optional int32[B].
- * algo      : 0 = auto (packed two-utterances-per-warp linear-domain path with per-utterance log-space fallback),
- *             1 = log-space only, 2 = packed path only (no fallback; for profiling),
+ * algo      : 0 = auto: packed two-utterances-per-warp linear-domain kernel at 8 frames per chunk; the utterances it
+ *                 flags (dynamic range, malformed rows) again at 2 frames per chunk; what is still flagged, in log space,
+ *             1 = log-space only, 2 = first packed pass only (no second tier, no fallback; for profiling),
  *             3 = the earlier one-utterance-per-warp linear-domain kernel with fallback (kept for A/B runs).
  * ------------------------------------------------------------------------------------------------------------------ */
 int mdd_ctc_loss_workspace_bytes(int T, int B, int C, int max_target_len, int algo, size_t* bytes);
