@@ -57,7 +57,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
     for src in sources():
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
-        if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(src), hdr_t):
+        inc = [os.path.join(CSRC, l.split('"')[1]) for l in open(src) if l.startswith('#include "') and l.split('"')[1].endswith(".cu")]
+        dep_t = max([os.path.getmtime(src), hdr_t] + [os.path.getmtime(f) for f in inc])    # a .cu may include another
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) > dep_t:
             continue
         log = open(obj + ".log", "w")
         extra = os.environ.get("MDD_NVCC_EXTRA", "").split()          # e.g. -DMDD_PAIR_TIMING for a debug build

@@ -40,6 +40,11 @@
 //    is still flagged in the same stream with torch's inf / NaN / zero_infinity semantics.
 //  * LOGITS instantiation: lp holds the output layer's logits, lse their row log-sum-exp (row_lse.cu); the emission
 //    is 2^(x log2 e - lse log2 e) and the gradient written is the one with respect to the logits.
+// This file is compiled twice so that the two halves of its instantiations build in parallel: as itself (log-prob
+// input, MDD_PAIR_TU_LOGITS 0, plus the public entry points) and through ctc_pair_logits.cu (logit input).
+#ifndef MDD_PAIR_TU_LOGITS
+#define MDD_PAIR_TU_LOGITS 0
+#endif
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -820,8 +825,7 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
 
 template <int NSL, bool REGBUF, int MAXR>
 int launch_cfg(const CtcParams& p, float* ws, cudaStream_t st) {
-    if (p.lse) return launch_tiers<NSL, REGBUF, MAXR, true>(p, ws, st);    // lp holds logits (mdd_ctc_loss_logits)
-    return launch_tiers<NSL, REGBUF, MAXR, false>(p, ws, st);
+    return launch_tiers<NSL, REGBUF, MAXR, MDD_PAIR_TU_LOGITS != 0>(p, ws, st);
 }
 
 template <int NSL>
@@ -845,6 +849,7 @@ int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
 
 }  // namespace
 
+#if !MDD_PAIR_TU_LOGITS
 #ifdef MDD_PAIR_TIMING
 extern "C" void mdd_debug_phase_cycles(unsigned long long* out, int reset) {
     cudaDeviceSynchronize();
@@ -864,17 +869,15 @@ size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
     const size_t n_ckpt = (size_t)T / KF + 2 * KF;
     return (size_t)((B + 1) / 2) * n_ckpt * 32 * (2 * nsl + 2) * 4;
 }
+#endif
 
-int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st) {
-    float* w = reinterpret_cast<float*>(ws);
-    static const char* tol_env = getenv("MDD_CTC_PBETA_TOL");
-    static int strict = env_int("MDD_CTC_STRICT_SQUASH", 0);
-    p.pbeta_tol = tol_env ? (float)atof(tol_env) : 3e-5f;
-    p.strict_squash = strict;
-    static int decay = env_int("MDD_CTC_DECAY_MAX", 76 + SHIFT);
-    p.decay_max = decay;
-    static int duo = env_int("MDD_CTC_DUO", 0);                  // two warps per pair (ctc_duo.cu)
-    if (duo && ctc_duo_supported(p.C, p.Lmax)) return launch_ctc_duo(p, ws, st);
+// the instantiations of this translation unit (log-prob input here, logit input in ctc_pair_logits.cu)
+#if MDD_PAIR_TU_LOGITS
+int launch_ctc_pair_tu_logits(const CtcParams& p, float* w, cudaStream_t st) {
+#else
+int launch_ctc_pair_tu_logits(const CtcParams& p, float* w, cudaStream_t st);
+static int launch_ctc_pair_tu(const CtcParams& p, float* w, cudaStream_t st) {
+#endif
     switch (pick_nsl(p.Lmax)) {
 #ifndef MDD_PAIR_ONLY8
         case 2: return launch_nsl<2>(p, w, st);
@@ -885,5 +888,20 @@ int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st) {
         default: return MDD_E_UNSUPPORTED;
     }
 }
+
+#if !MDD_PAIR_TU_LOGITS
+int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st) {
+    float* w = reinterpret_cast<float*>(ws);
+    static const char* tol_env = getenv("MDD_CTC_PBETA_TOL");
+    static int strict = env_int("MDD_CTC_STRICT_SQUASH", 0);
+    p.pbeta_tol = tol_env ? (float)atof(tol_env) : 3e-5f;
+    p.strict_squash = strict;
+    static int decay = env_int("MDD_CTC_DECAY_MAX", 76 + SHIFT);
+    p.decay_max = decay;
+    static int duo = env_int("MDD_CTC_DUO", 0);                  // two warps per pair (ctc_duo.cu)
+    if (duo && !p.lse && ctc_duo_supported(p.C, p.Lmax)) return launch_ctc_duo(p, ws, st);
+    return p.lse ? launch_ctc_pair_tu_logits(p, w, st) : launch_ctc_pair_tu(p, w, st);
+}
+#endif
 
 }  // namespace mdd
