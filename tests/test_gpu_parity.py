@@ -335,6 +335,41 @@ def test_ctc_from_logits_module_train_step(M):
         np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=LOSS_RTOL)
 
 
+def test_ctc_from_logits_api_edges(M):
+    """(T,C) input, fp64 logits, lengths as tuples, CPU logits in, zero-length targets under 'mean', zero_infinity."""
+    from mddctc.loss import ctc_loss_from_logits
+    F = torch.nn.functional
+    g = torch.Generator().manual_seed(14)
+    x2 = (torch.randn(50, 9, generator=g) * 2).requires_grad_(True)                   # (T, C): one utterance
+    tg1 = torch.randint(1, 9, (6,), generator=g)
+    got = ctc_loss_from_logits(x2, tg1, (50,), (6,), reduction="sum")
+    got.backward()
+    xr = x2.detach().clone().requires_grad_(True)
+    want = F.ctc_loss(torch.log_softmax(xr, -1), tg1, (50,), (6,), reduction="sum")
+    want.backward()
+    np.testing.assert_allclose(float(got.detach()), float(want.detach()), rtol=LOSS_RTOL)
+    assert x2.grad.shape == xr.grad.shape and float((x2.grad - xr.grad).abs().max()) <= GRAD_ATOL
+    T, B, C, L = 80, 5, 11, 7
+    x = torch.randn(T, B, C, generator=g, dtype=torch.float64) * 2
+    tg = torch.randint(1, C, (B, L), generator=g)
+    il, tl = torch.tensor([80, 64, 80, 12, 5]), torch.tensor([7, 0, 3, 7, 7])                # row 4 infeasible, row 1 empty
+    for red in ("mean", "sum", "none"):
+        for zi in (False, True):
+            got = ctc_loss_from_logits(x.cuda(), tg.cuda(), il, tl, reduction=red, zero_infinity=zi)
+            want = F.ctc_loss(torch.log_softmax(x, -1), tg, il, tl, reduction=red, zero_infinity=zi)
+            assert got.dtype == torch.float64 and got.shape == want.shape
+            np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=LOSS_RTOL)
+    xc = x.float().requires_grad_(True)                                                   # CPU tensor in, CPU grad out
+    loss = ctc_loss_from_logits(xc, tg, il, tl, reduction="sum", zero_infinity=True)
+    loss.backward()
+    assert not loss.is_cuda and not xc.grad.is_cuda
+    xr = x.float().clone().requires_grad_(True)
+    F.ctc_loss(torch.log_softmax(xr, -1), tg, il, tl, reduction="sum", zero_infinity=True).backward()
+    assert float((xc.grad - xr.grad).abs().max()) <= GRAD_ATOL
+    with pytest.raises(RuntimeError):
+        ctc_loss_from_logits(x.cuda(), tg.cuda(), torch.tensor([81, 1, 1, 1, 1]), tl)
+
+
 def test_ctc_logits_full_config3_properties(M):
     """Config 3 at full size (T=1000, B=4096, C=42, L=120) through size-independent properties: the logit gradient's
     rows sum to zero, the loss equals the log-prob path's on log_softmax of the same logits, two launches agree bitwise,
