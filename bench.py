@@ -235,13 +235,21 @@ def run_ours(args):
     tg_d, il_d, tl_d = torch.empty_like(tg), torch.empty_like(il), torch.empty_like(tl)
     loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
 
+    from mddctc.loss import ctc_loss_streamed
+
     def step_e2e():
-        lp_d.copy_(lp_h, non_blocking=True)
         tg_d.copy_(tg_h, non_blocking=True)
         il_d.copy_(il_h, non_blocking=True)
         tl_d.copy_(tl_h, non_blocking=True)
-        ctc_loss_raw(lp_d, tg_d, il_d, tl_d, want_grad=True, grad_scalar=inv_b, validate=False, loss_sum=loss_buf, nll=nll,
-                     grad=grad, status=status, algo=args.algo)
+        if args.e2e_slices > 1:
+            # the public host-buffer call: batch slices cross PCIe on a side stream while the previous slice computes
+            total, _, _ = ctc_loss_streamed(lp_h, tg_d, il_d, tl_d, slices=args.e2e_slices, grad_scalar=inv_b,
+                                            staging=lp_d, algo=args.algo)
+            loss_buf.copy_(total)
+        else:
+            lp_d.copy_(lp_h, non_blocking=True)
+            ctc_loss_raw(lp_d, tg_d, il_d, tl_d, want_grad=True, grad_scalar=inv_b, validate=False, loss_sum=loss_buf,
+                         nll=nll, grad=grad, status=status, algo=args.algo)
         if world > 1:
             dist.all_reduce(loss_buf)
         loss_host.copy_(loss_buf, non_blocking=True)
@@ -419,6 +427,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--algo", type=int, default=0)
+    ap.add_argument("--e2e-slices", type=int, default=4,
+                    help="batch slices of the end-to-end leg (H2D of slice k+1 overlaps the kernels of slice k); 1 = one copy")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--extras", action="store_true", help="also time joint decode and greedy+MDD alignment")
     args = ap.parse_args()

@@ -93,7 +93,7 @@ class PostOut(C.Structure):
 
 
 EXPORTS = ["mdd_version", "mdd_error_string", "mdd_launch_count", "mdd_launch_count_reset",
-           "mdd_ctc_loss_workspace_bytes", "mdd_ctc_loss", "mdd_ctc_loss_logits", "mdd_row_lse", "mdd_ctc_scale_grad", "mdd_greedy_decode", "mdd_collapse", "mdd_post_align", "mdd_corpus_counts",
+           "mdd_ctc_loss_workspace_bytes", "mdd_ctc_loss", "mdd_ctc_loss_logits", "mdd_row_lse", "mdd_copy_h2d_2d", "mdd_ctc_scale_grad", "mdd_greedy_decode", "mdd_collapse", "mdd_post_align", "mdd_corpus_counts",
            "mdd_edit_align_workspace_bytes", "mdd_edit_align", "mdd_beam_search_workspace_bytes", "mdd_beam_search",
            "mdd_exp_transpose", "mdd_prefix_init", "mdd_prefix_score", "mdd_prefix_advance"]
 
@@ -122,6 +122,7 @@ def lib():
     L.mdd_ctc_loss_logits.argtypes = [vp, i, i, i, i64, i64, vp, i64, vp, vp, i, i, i, vp, f, vp, vp, vp, vp, vp, vp, i,
                                       vp, sz, vp]
     L.mdd_row_lse.argtypes = [vp, i, i, i, i64, i64, vp, vp, vp]
+    L.mdd_copy_h2d_2d.argtypes = [vp, sz, vp, sz, sz, sz, vp]
     L.mdd_ctc_scale_grad.argtypes = [vp, i, i, i, vp, f, vp]
     L.mdd_greedy_decode.argtypes = [vp, i, i, i, vp, i, vp, vp, vp, i, vp, vp]
     L.mdd_collapse.argtypes = [vp, i, i, vp, i, vp, vp, i, vp, vp]

@@ -33,3 +33,15 @@ def stream_ptr(dev: torch.device) -> int:
 
 def ptr(t) -> int:
     return 0 if t is None else t.data_ptr()
+
+
+_copy_streams = {}
+
+
+def copy_stream(dev: torch.device) -> "torch.cuda.Stream":
+    """A per-device side stream for host -> device transfers that overlap the kernels of the current stream."""
+    st = _copy_streams.get(dev.index)
+    if st is None:
+        st = torch.cuda.Stream(device=dev)
+        _copy_streams[dev.index] = st
+    return st

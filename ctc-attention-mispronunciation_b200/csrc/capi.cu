@@ -147,6 +147,18 @@ extern "C" int mdd_ctc_loss_logits(const float* logits, int T, int B, int C, int
                          status, row_lse, argmax, algo, workspace, workspace_bytes, stream);
 }
 
+extern "C" int mdd_copy_h2d_2d(void* dst, size_t dst_pitch, const void* src_host, size_t src_pitch, size_t width_bytes,
+                               size_t height, mdd_stream_t stream) {
+    if (width_bytes == 0 || height == 0) return MDD_OK;
+    if (!dst || !src_host || dst_pitch < width_bytes || src_pitch < width_bytes) return MDD_E_ARG;
+    if (cudaMemcpy2DAsync(dst, dst_pitch, src_host, src_pitch, width_bytes, height, cudaMemcpyHostToDevice,
+                          (cudaStream_t)stream) != cudaSuccess) {
+        cudaGetLastError();
+        return MDD_E_CUDA;
+    }
+    return MDD_OK;
+}
+
 extern "C" int mdd_ctc_scale_grad(float* grad, int T, int B, int C, const float* scale, float scalar,
                                   mdd_stream_t stream) {
     if (!grad || T < 0 || B < 0 || C <= 0) return MDD_E_ARG;

@@ -111,6 +111,13 @@ int mdd_ctc_loss_logits(const float* logits, int T, int B, int C, int64_t stride
 int mdd_row_lse(const float* logits, int T, int B, int C, int64_t stride_t, int64_t stride_b, float* row_lse,
                 uint8_t* argmax, mdd_stream_t stream);
 
+/* Host -> device copy of a batch slice of a (T,B,C) array: `height` rows of `width_bytes`, row pitches in bytes
+ * (cudaMemcpy2DAsync on `stream`; `src_host` should be page-locked).  Lets a caller whose log-probs live in host memory
+ * (the reference keeps them there for decoding, infer.py:300) overlap the transfer of one batch slice with the kernels of
+ * the previous one: mddctc.loss.ctc_loss_streamed. */
+int mdd_copy_h2d_2d(void* dst, size_t dst_pitch, const void* src_host, size_t src_pitch, size_t width_bytes,
+                    size_t height, mdd_stream_t stream);
+
 /* grad[t,b,c] *= scale[b] * scalar   (autograd backward when the upstream gradient was not known in forward). */
 int mdd_ctc_scale_grad(float* grad, int T, int B, int C, const float* scale, float scalar, mdd_stream_t stream);
 

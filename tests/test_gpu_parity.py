@@ -335,6 +335,31 @@ def test_ctc_from_logits_module_train_step(M):
         np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=LOSS_RTOL)
 
 
+def test_ctc_loss_streamed_matches_whole_batch(M):
+    """Host-resident log-probs in batch slices over a side stream: per-utterance results are those of the one-shot call."""
+    from mddctc.loss import ctc_loss_raw, ctc_loss_streamed
+    g = torch.Generator().manual_seed(15)
+    T, B, C, L = 300, 37, 42, 40
+    lp_h = torch.log_softmax(torch.randn(T, B, C, generator=g), -1).pin_memory()
+    tg = torch.randint(1, C, (B, L), generator=g).cuda()
+    il = torch.randint(150, T + 1, (B,), generator=g).cuda()
+    tl = torch.randint(0, L + 1, (B,), generator=g).cuda()
+    nll, grad, _ = ctc_loss_raw(lp_h.cuda(), tg, il, tl, grad_scalar=0.5)
+    for slices in (1, 4, 5):
+        total, nll_s, grads = ctc_loss_streamed(lp_h, tg, il, tl, slices=slices, grad_scalar=0.5)
+        gs = torch.cat(grads, dim=1)
+        if slices == 1:
+            assert torch.equal(nll_s, nll) and torch.equal(gs, grad)
+        else:
+            # an utterance's chunk boundaries (hence its rounding) follow its partner in the warp when the two differ in
+            # length, and slicing changes the partners: equal to the last bits, not bitwise
+            np.testing.assert_allclose(nll_s.cpu().numpy(), nll.cpu().numpy(), rtol=1e-6)
+            assert float((gs - grad).abs().max()) < 2e-6
+        np.testing.assert_allclose(float(total), float(nll.sum()), rtol=1e-6)
+    with pytest.raises(RuntimeError):
+        ctc_loss_streamed(lp_h.cuda(), tg, il, tl)
+
+
 def test_ctc_from_logits_api_edges(M):
     """(T,C) input, fp64 logits, lengths as tuples, CPU logits in, zero-length targets under 'mean', zero_infinity."""
     from mddctc.loss import ctc_loss_from_logits
