@@ -4,6 +4,18 @@
 
 namespace mdd {
 int64_t g_launch_count = 0;
+
+int sm_count() {
+    static int cached[64];                                       // per device: one process may drive several GPUs
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return kNumSM;
+    if (!cached[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = kNumSM;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
 }
 using namespace mdd;
 
@@ -24,12 +36,10 @@ extern "C" int64_t mdd_launch_count(void) { return g_launch_count; }
 extern "C" void mdd_launch_count_reset(void) { g_launch_count = 0; }
 
 namespace {
-// which linear-domain kernel serves this shape: the pair kernel where it applies, else the scalar one (C = 64)
+// which kernel serves this shape: 1 = the packed fp32 pair kernel where it applies, 0 = the fp64 kernel alone
 int ctc_kernel_choice(int C, int Lmax, int algo) {
     if (algo == 1) return 0;
-    if (algo != 3 && ctc_pair_supported(C, Lmax)) return 1;
-    if (algo != 2 && ctc_fast_supported(C, Lmax)) return 2;
-    return 0;
+    return ctc_pair_supported(C, Lmax) ? 1 : 0;
 }
 struct CtcWs {
     size_t off_offsets, off_flags, off_list, off_ckpt, off_fast, total;
@@ -41,18 +51,17 @@ CtcWs ctc_ws_layout(int T, int B, int C, int Lmax, int algo) {
     w.off_flags = o;   o = align_up(o + (size_t)B * 4, 256);
     w.off_list = o;    o = align_up(o + (size_t)(B + 1) * 4, 256);     // second tier: flagged utterances + their count
     w.off_ckpt = o;
-    const int kern = ctc_kernel_choice(C, Lmax, algo);           // 0 log-space only, 1 pair kernel, 2 scalar kernel
-    if (algo != 2) o = align_up(o + ctc_log_ckpt_bytes(T, B, Lmax), 256);
+    const int kern = ctc_kernel_choice(C, Lmax, algo);           // 0 fp64 kernel only, 1 pair kernel
+    if (algo != 2) o = align_up(o + ctc_exact_ckpt_bytes(T, B, Lmax), 256);
     w.off_fast = o;
     if (kern == 1) o = align_up(o + ctc_pair_ws_bytes(T, B, Lmax), 256);
-    if (kern == 2) o = align_up(o + ctc_fast_ws_bytes(T, B, Lmax), 256);
     w.total = o;
     return w;
 }
 }  // namespace
 
 extern "C" int mdd_ctc_loss_workspace_bytes(int T, int B, int C, int max_target_len, int algo, size_t* bytes) {
-    if (!bytes || T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || algo < 0 || algo > 3)
+    if (!bytes || T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || algo < 0 || algo > 2)
         return MDD_E_ARG;
     *bytes = ctc_ws_layout(T, B, C, max_target_len, algo).total;
     return MDD_OK;
@@ -67,7 +76,7 @@ int ctc_loss_impl(const float* log_probs, int T, int B, int C, int64_t stride_t,
                   int32_t* status, float* row_lse, uint8_t* argmax, int algo, void* workspace,
                   size_t workspace_bytes, mdd_stream_t stream) {
     if (T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || blank < 0 || blank >= C || algo < 0 ||
-        algo > 3)
+        algo > 2)
         return MDD_E_ARG;
     if (B == 0) return MDD_OK;
     if ((!log_probs && T > 0) || !input_lengths || !target_lengths || !nll || (!targets && max_target_len > 0))
@@ -98,22 +107,21 @@ int ctc_loss_impl(const float* log_probs, int T, int B, int C, int64_t stride_t,
     int kern = T > 0 ? ctc_kernel_choice(C, max_target_len, algo) : 0;
     if (algo == 2 && kern != 1) return MDD_E_UNSUPPORTED;
     if (row_lse) {
-        if (kern == 2) kern = 0;                                 // the scalar kernel reads log-probs only
         rc = launch_row_lse(log_probs, T, B, C, stride_t, stride_b, row_lse, argmax, st);
         if (rc) return rc;
     }
     if (kern) {
-        // flags[b] != 0 on return -> utterance needs the log-space path
-        rc = kern == 2 ? launch_ctc_fast(p, ws + w.off_fast, st) : launch_ctc_pair(p, ws + w.off_fast, st);
+        // flags[b] != 0 on return -> the utterance is redone by the fp64 kernel
+        rc = launch_ctc_pair(p, ws + w.off_fast, st);
         if (rc) return rc;
-        if (algo == 0 || algo == 3) {
+        if (algo == 0) {
             p.only_flagged = 1;
-            rc = launch_ctc_log(p, st);
+            rc = launch_ctc_exact(p, st);
             if (rc) return rc;
         }
     } else {
         p.only_flagged = 0;
-        rc = launch_ctc_log(p, st);
+        rc = launch_ctc_exact(p, st);
         if (rc) return rc;
     }
     if (loss_sum) {
@@ -141,7 +149,6 @@ extern "C" int mdd_ctc_loss_logits(const float* logits, int T, int B, int C, int
                                    float* loss_sum, int32_t* status, float* row_lse, uint8_t* argmax, int algo,
                                    void* workspace, size_t workspace_bytes, mdd_stream_t stream) {
     if (!row_lse && (long long)T * B > 0) return MDD_E_ARG;
-    if (algo == 3) return MDD_E_UNSUPPORTED;
     return ctc_loss_impl(logits, T, B, C, stride_t, stride_b, targets, tgt_stride, input_lengths, target_lengths,
                          max_target_len, blank, zero_infinity, grad_out, grad_out_scalar, nll, grad_logits, loss_sum,
                          status, row_lse, argmax, algo, workspace, workspace_bytes, stream);

@@ -4,6 +4,8 @@
 #include <math_constants.h>
 #include <stdint.h>
 
+#include <algorithm>
+
 #include "../../include/mddctc.h"
 
 namespace mdd {
@@ -16,7 +18,8 @@ extern int64_t g_launch_count;   // defined in capi.cu
         if (cudaPeekAtLastError() != cudaSuccess) { cudaGetLastError(); return MDD_E_CUDA; } \
     } while (0)
 
-constexpr int kNumSM = 148;   // B200
+constexpr int kNumSM = 148;   // B200 (grid sizing of the streaming kernels)
+int sm_count();               // SMs of the current device (capi.cu)
 
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }

@@ -898,8 +898,6 @@ int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st) {
     p.strict_squash = strict;
     static int decay = env_int("MDD_CTC_DECAY_MAX", 76 + SHIFT);
     p.decay_max = decay;
-    static int duo = env_int("MDD_CTC_DUO", 0);                  // two warps per pair (ctc_duo.cu)
-    if (duo && !p.lse && ctc_duo_supported(p.C, p.Lmax)) return launch_ctc_duo(p, ws, st);
     return p.lse ? launch_ctc_pair_tu_logits(p, w, st) : launch_ctc_pair_tu(p, w, st);
 }
 #endif

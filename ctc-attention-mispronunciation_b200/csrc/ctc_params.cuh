@@ -23,8 +23,8 @@ struct CtcParams {
     float* nll;               // [B]
     float* grad;              // (T,B,C) contiguous or null
     int32_t* status;          // [B] or null
-    // log-space kernel
-    float* ckpt;              // [B][n_ckpt][2*Lmax+1]
+    // fp64 kernel (ctc_exact.cu)
+    float* ckpt;              // [B][n_ckpt][2*Lmax+1] doubles
     int K, n_ckpt;
     int only_flagged;         // process only utterances with flags[b] != 0
     int32_t* flags;           // [B] fast path -> fallback requests
@@ -39,20 +39,14 @@ struct CtcParams {
     int decay_max;            // largest per-chunk decay (bits) of the lanes holding the bulk of alpha
 };
 
-int ctc_log_chunk(int Lmax);
-size_t ctc_log_ckpt_bytes(int T, int B, int Lmax);
+// fp64 linear-domain kernel, one CTA per utterance (ctc_exact.cu): robust path and per-utterance fallback
+int ctc_exact_chunk(int Lmax);
+size_t ctc_exact_ckpt_bytes(int T, int B, int Lmax);
 int launch_tgt_offsets(const int64_t* tgt_len, int B, int64_t* off, cudaStream_t st);
-int launch_ctc_log(CtcParams p, cudaStream_t st);
-
-// rescaled linear-domain fast path (ctc_fast.cu)
-bool ctc_fast_supported(int C, int Lmax);
-size_t ctc_fast_ws_bytes(int T, int B, int Lmax);
-int launch_ctc_fast(CtcParams p, void* ws, cudaStream_t st);
+int launch_ctc_exact(CtcParams p, cudaStream_t st);
 
 // two utterances per warp, packed FP32 (ctc_pair.cu): the default fast path
 bool ctc_pair_supported(int C, int Lmax);
-bool ctc_duo_supported(int C, int Lmax);          // two warps per pair (ctc_duo.cu): same workspace as the pair kernel
-int launch_ctc_duo(CtcParams p, void* ws, cudaStream_t st);
 size_t ctc_pair_ws_bytes(int T, int B, int Lmax);
 int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st);
 

@@ -1,17 +1,23 @@
 """CTC prefix scorer for CTC/attention joint beam decoding (BASELINE.json north_star).
 
 The reference has no attention decoder and no such function; its nearest code is the (prBlank, prNonBlank, prTotal)
-recursion of egs/attention_aug/utils/BeamSearch.py:52-66,99-125.  This module provides the standard
-Watanabe/ESPnet-style scorer on the CUDA kernels (mdd_prefix_init / mdd_prefix_score / mdd_prefix_advance) and a small
-joint beam-search driver that fuses it with externally supplied attention log-probabilities:
+recursion and the sort + [:beamWidth] of egs/attention_aug/utils/BeamSearch.py:52-66,99-125.  This module provides the
+standard Watanabe/ESPnet-style scorer on the CUDA kernels (mdd_prefix_init / mdd_prefix_score / mdd_prefix_select /
+mdd_prefix_advance) and the label-synchronous joint beam search that fuses it with externally supplied attention
+log-probabilities:
 
-    score(g.c) = ctc_weight * (psi(g.c) - psi(g)) + (1 - ctc_weight) * att_logp[c]
+    score(g.c) = score(g) + ctc_weight * (psi(g.c) - psi(g)) + (1 - ctc_weight) * att_logp[c]
+
+Scores and CTC state are fp64 on the device (see csrc/prefix_score.cu); a decoding step is three kernel launches
+(score, select, advance) and whatever the caller's attention decoder does -- no torch.topk / gather in between.
 """
 from __future__ import annotations
 
 import torch
 
 from . import _lib, _rt
+
+LIVE, FINISHED, DEAD = 0, 1, 2
 
 
 class CTCPrefixScorer:
@@ -25,73 +31,101 @@ class CTCPrefixScorer:
         self.lens = None if input_lengths is None else input_lengths.to(device=self.dev, dtype=torch.int64).contiguous()
         self._L = _lib.lib()
 
-    def initial_state(self):
-        r = torch.empty((self.B, self.W, self.T, 2), dtype=torch.float32, device=self.dev)
-        _lib.check(self._L.mdd_prefix_init(self.x.data_ptr(), self.T, self.B, self.C, _rt.ptr(self.lens), self.blank,
-                                           self.W, r.data_ptr(), _rt.stream_ptr(self.dev)), "mdd_prefix_init")
-        return {"r": r, "last": torch.full((self.B, self.W), -1, dtype=torch.int32, device=self.dev),
-                "glen": torch.zeros((self.B, self.W), dtype=torch.int32, device=self.dev),
-                "psi": torch.zeros((self.B, self.W), dtype=torch.float32, device=self.dev)}
+    def initial_state(self, max_len=None, all_slots_live=False):
+        """The empty prefix.  By default only slot 0 of every utterance is live (a beam search starts from ONE empty
+        hypothesis); ``all_slots_live`` makes every slot an independent empty hypothesis (scoring given prefixes)."""
+        B, W, T, dev = self.B, self.W, self.T, self.dev
+        r = torch.empty((B, W, T, 2), dtype=torch.float64, device=dev)
+        _lib.check(self._L.mdd_prefix_init(self.x.data_ptr(), T, B, self.C, _rt.ptr(self.lens), self.blank, W,
+                                           r.data_ptr(), _rt.stream_ptr(dev)), "mdd_prefix_init")
+        flag = torch.full((B, W), LIVE if all_slots_live else DEAD, dtype=torch.int32, device=dev)
+        score = torch.full((B, W), 0.0 if all_slots_live else -float("inf"), dtype=torch.float64, device=dev)
+        flag[:, 0] = LIVE
+        score[:, 0] = 0.0
+        return {"r": r, "last": torch.full((B, W), -1, dtype=torch.int32, device=dev),
+                "glen": torch.zeros((B, W), dtype=torch.int32, device=dev),
+                "psi": torch.zeros((B, W), dtype=torch.float64, device=dev),          # psi(empty prefix) = log 1
+                "score": score, "flag": flag,
+                "tokens": torch.full((B, W, max_len or T), -1, dtype=torch.int32, device=dev)}
 
     def score(self, state):
-        """psi[B,W,C] = log p_ctc(g.c, ...) for every candidate label, psi_eos[B,W] = log p_ctc(g)."""
-        psi = torch.empty((self.B, self.W, self.C), dtype=torch.float32, device=self.dev)
-        eos = torch.empty((self.B, self.W), dtype=torch.float32, device=self.dev)
+        """psi[B,W,C] = log p_ctc(g.c, ...) for every candidate label, psi_eos[B,W] = log p_ctc(g) (fp64).
+        Finished / dead hypotheses are not extended (all -inf)."""
+        psi = torch.empty((self.B, self.W, self.C), dtype=torch.float64, device=self.dev)
+        eos = torch.empty((self.B, self.W), dtype=torch.float64, device=self.dev)
         _lib.check(self._L.mdd_prefix_score(self.x.data_ptr(), self.T, self.B, self.C, _rt.ptr(self.lens), self.blank,
                                             self.W, state["r"].data_ptr(), state["last"].data_ptr(),
-                                            state["glen"].data_ptr(), psi.data_ptr(), eos.data_ptr(),
-                                            _rt.stream_ptr(self.dev)), "mdd_prefix_score")
+                                            state["glen"].data_ptr(), state["flag"].data_ptr(), psi.data_ptr(),
+                                            eos.data_ptr(), _rt.stream_ptr(self.dev)), "mdd_prefix_score")
         return psi, eos
 
-    def advance(self, state, sel_hyp, sel_label, keep=None, psi=None):
-        """New state for the chosen (parent hypothesis, label) pairs.  keep[b,w] False leaves slot w untouched
-        (finished hypotheses)."""
+    def select(self, state, psi, psi_eos, att_logp, ctc_weight=0.3, eos=None):
+        """One beam step: the W best of the W*C candidates of every utterance.  Returns the new state WITHOUT its CTC
+        recursion state (call advance) plus (sel_hyp, sel_label)."""
+        B, W, C, dev = self.B, self.W, self.C, self.dev
+        att = att_logp.to(device=dev, dtype=torch.float32).contiguous()
+        if tuple(att.shape) != (B, W, C):
+            raise RuntimeError("att_logp must be (B, W, C)")
+        max_len = state["tokens"].shape[2]
+        new = {"last": torch.empty_like(state["last"]), "glen": torch.empty_like(state["glen"]),
+               "psi": torch.empty_like(state["psi"]), "score": torch.empty_like(state["score"]),
+               "flag": torch.empty_like(state["flag"]), "tokens": torch.empty_like(state["tokens"])}
+        sel_hyp = torch.empty((B, W), dtype=torch.int32, device=dev)
+        rc = self._L.mdd_prefix_select(B, W, C, self.blank, -1 if eos is None else int(eos), float(ctc_weight), max_len,
+                                       psi.data_ptr(), psi_eos.data_ptr(), att.data_ptr(), state["score"].data_ptr(),
+                                       state["psi"].data_ptr(), state["glen"].data_ptr(), state["flag"].data_ptr(),
+                                       state["tokens"].data_ptr(), sel_hyp.data_ptr(), new["last"].data_ptr(),
+                                       new["score"].data_ptr(), new["psi"].data_ptr(), new["glen"].data_ptr(),
+                                       new["flag"].data_ptr(), new["tokens"].data_ptr(), _rt.stream_ptr(dev))
+        _lib.check(rc, "mdd_prefix_select")
+        return new, sel_hyp, new["last"]
+
+    def advance(self, state, sel_hyp, sel_label, new_flag=None):
+        """CTC recursion state r (B,W,T,2) of the chosen (parent hypothesis, label) pairs; slots whose new flag is
+        non-zero (finished / dead) or whose parent is -1 are left untouched."""
         sel_hyp = sel_hyp.to(device=self.dev, dtype=torch.int32).contiguous()
         sel_label = sel_label.to(device=self.dev, dtype=torch.int32).contiguous()
         r_new = torch.empty_like(state["r"])
         _lib.check(self._L.mdd_prefix_advance(self.x.data_ptr(), self.T, self.B, self.C, _rt.ptr(self.lens), self.blank,
                                               self.W, state["r"].data_ptr(), state["last"].data_ptr(),
                                               state["glen"].data_ptr(), sel_hyp.data_ptr(), sel_label.data_ptr(),
-                                              r_new.data_ptr(), _rt.stream_ptr(self.dev)), "mdd_prefix_advance")
-        idx = sel_hyp.long().clamp_min(0)
-        last = sel_label.clone()
-        glen = torch.gather(state["glen"], 1, idx) + 1
-        new_psi = state["psi"] if psi is None else torch.gather(psi.reshape(self.B, -1), 1,
-                                                               idx * self.C + sel_label.long().clamp_min(0))
-        if keep is not None:
-            keep = keep.to(self.dev)
-            r_new = torch.where(keep[:, :, None, None], r_new, state["r"])
-            last = torch.where(keep, last, state["last"])
-            glen = torch.where(keep, glen, state["glen"])
-            new_psi = torch.where(keep, new_psi, state["psi"])
-        return {"r": r_new, "last": last, "glen": glen.to(torch.int32), "psi": new_psi}
+                                              _rt.ptr(new_flag), r_new.data_ptr(), _rt.stream_ptr(self.dev)),
+                   "mdd_prefix_advance")
+        return r_new
+
+    def extend(self, state, labels):
+        """Append labels[B,W] (int, -1 = leave the slot) to the hypotheses in place of a beam step: the state of
+        g.c for given prefixes (used to score known label sequences)."""
+        labels = labels.to(device=self.dev, dtype=torch.int32).contiguous()
+        psi, _ = self.score(state)
+        hyp = torch.arange(self.W, dtype=torch.int32, device=self.dev)[None, :].expand(self.B, self.W).contiguous()
+        keep = labels >= 0
+        hyp = torch.where(keep, hyp, torch.full_like(hyp, -1))
+        r_new = self.advance(state, hyp, labels)
+        new = dict(state)
+        new["r"] = torch.where(keep[:, :, None, None], r_new, state["r"])
+        new["last"] = torch.where(keep, labels, state["last"])
+        new["glen"] = state["glen"] + keep.to(torch.int32)
+        new["psi"] = torch.where(keep, torch.gather(psi, 2, labels.clamp_min(0).long()[..., None])[..., 0], state["psi"])
+        return new
 
 
 def joint_beam_search(log_probs, input_lengths, att_logp_fn, beam=10, ctc_weight=0.3, max_len=None, blank=0, eos=None):
     """Label-synchronous joint CTC/attention beam search (BASELINE config 4 shape: beam 10, CTC weight 0.3).
 
-    att_logp_fn(step, prefixes[B,W,step]) -> (B,W,C) attention-decoder log-probs (synthetic in the benchmarks, since
-    the reference has no attention decoder).  Ends after max_len steps; returns (tokens[B,W,max_len], scores[B,W]).
+    att_logp_fn(step, state) -> (B,W,C) attention-decoder log-probs for the hypotheses of ``state`` (its "tokens"
+    (B,W,max_len) int32, "last" and "glen" describe them; synthetic in the benchmarks, since the reference has no
+    attention decoder).  With ``eos`` a hypothesis ends when eos is chosen (scored with psi_eos = log p_ctc(g)) and is
+    carried unchanged from then on; without it every hypothesis runs to max_len labels.
+    Returns (tokens[B,W,max_len] int32 (-1 padded), scores[B,W] fp64, lengths[B,W] int32, flags[B,W] int32), best first.
     """
     scorer = CTCPrefixScorer(log_probs, input_lengths, blank=blank, beam=beam)
-    B, W, C, dev = scorer.B, beam, scorer.C, scorer.dev
     max_len = max_len or scorer.T
-    state = scorer.initial_state()
-    tokens = torch.zeros((B, W, max_len), dtype=torch.int64, device=dev)
-    score = torch.full((B, W), -float("inf"), device=dev)
-    score[:, 0] = 0.0                                    # a single live (empty) hypothesis per utterance
+    state = scorer.initial_state(max_len=max_len)
     for step in range(max_len):
-        psi, _ = scorer.score(state)
-        att = att_logp_fn(step, tokens[:, :, :step])
-        delta = psi - state["psi"][:, :, None]
-        cand = score[:, :, None] + ctc_weight * delta + (1.0 - ctc_weight) * att
-        cand[:, :, blank] = -float("inf")
-        if eos is not None:
-            cand[:, :, eos] = -float("inf")
-        top, flat = cand.reshape(B, W * C).topk(W, dim=1)
-        sel_h, sel_l = (flat // C).to(torch.int32), (flat % C).to(torch.int32)
-        state = scorer.advance(state, sel_h, sel_l, psi=psi)
-        tokens = torch.gather(tokens, 1, sel_h.long()[:, :, None].expand(B, W, max_len)).clone()
-        tokens[:, :, step] = sel_l.long()
-        score = top
-    return tokens, score
+        psi, psi_eos = scorer.score(state)
+        att = att_logp_fn(step, state)
+        new, sel_h, sel_l = scorer.select(state, psi, psi_eos, att, ctc_weight=ctc_weight, eos=eos)
+        new["r"] = scorer.advance(state, sel_h, sel_l, new_flag=new["flag"])
+        state = new
+    return state["tokens"], state["score"], state["glen"], state["flag"]

@@ -71,10 +71,10 @@ void mdd_launch_count_reset(void);
  * grad      : (T,B,C) contiguous fp32 out, or NULL for loss only.  Rows t >= input_lengths[b] are written as 0.
  * loss_sum  : optional fp32 scalar out = sum_b nll[b] (deterministic fixed-order tree), e.g. an NCCL send buffer.
  * status    : optional int32[B].
- * algo      : 0 = auto: packed two-utterances-per-warp linear-domain kernel at 8 frames per chunk; the utterances it
- *                 flags (dynamic range, malformed rows) again at 2 frames per chunk; what is still flagged, in log space,
- *             1 = log-space only, 2 = first packed pass only (no second tier, no fallback; for profiling),
- *             3 = the earlier one-utterance-per-warp linear-domain kernel with fallback (kept for A/B runs).
+ * algo      : 0 = auto: packed two-utterances-per-warp fp32 linear-domain kernel at 8 frames per chunk; the utterances
+ *                 it flags (dynamic range, malformed rows) again at 2 frames per chunk; what is still flagged by the
+ *                 fp64 linear-domain kernel (one CTA per utterance, exact to the rounding of the fp32 outputs),
+ *             1 = fp64 kernel only, 2 = first packed pass only (no second tier, no fallback; for profiling).
  * ------------------------------------------------------------------------------------------------------------------ */
 int mdd_ctc_loss_workspace_bytes(int T, int B, int C, int max_target_len, int algo, size_t* bytes);
 int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t stride_t, int64_t stride_b,
@@ -97,7 +97,7 @@ int mdd_ctc_loss(const float* log_probs, int T, int B, int C, int64_t stride_t, 
  *               gradient through log_softmax (its rows sum to zero).  Rows t >= input_lengths[b] are 0.
  * row_lse     : fp32 (T,B) out, required: log sum_c exp(logits[t,b,c]); log_probs[t,b,c] = logits[t,b,c] - row_lse[t,b].
  * argmax      : uint8 (T,B) out or NULL: frame arg-max (first maximum wins), ready for mdd_collapse.
- * algo        : 0, 1 or 2 (3 is not available on logits).  Workspace: mdd_ctc_loss_workspace_bytes.
+ * algo        : 0, 1 or 2.  Workspace: mdd_ctc_loss_workspace_bytes.
  * One pre-pass kernel streams the logits once (4*C B/frame) and writes 5 B/frame; no (T,B,C) log-prob array and no
  * log_softmax backward pass exist.
  * ------------------------------------------------------------------------------------------------------------------ */
@@ -232,20 +232,34 @@ int mdd_exp_transpose(const float* log_probs, int T, int B, int C, float* probs,
  * absent from the reference as a function -- nearest reference code is BeamSearch.py:52-66,99-125).
  *
  * x      : (T,B,C) fp32 log-probs contiguous; input_lengths int64[B] or NULL.
- * r_prev : (B,W,T,2) fp32 [r_n, r_b] per hypothesis (mdd_prefix_init fills the empty-prefix state for w = 0..W-1).
+ * Arithmetic and state are fp64 (log-likelihoods of magnitude |nll|; the beam is chosen by their differences).
+ * r_prev : (B,W,T,2) fp64 [r_n, r_b] per hypothesis (mdd_prefix_init fills the empty-prefix state for w = 0..W-1).
  * last   : int32 (B,W) last label of each hypothesis (-1 = empty), glen int32 (B,W) hypothesis lengths.
- * psi    : (B,W,C) fp32 out: log p_ctc(g.c, ...); psi[...,blank] = -inf.   psi_eos (B,W) = log p_ctc(g) (optional).
+ * skip   : optional int32 (B,W): non-zero = hypothesis is finished (1) or dead (2); it is not extended (psi = -inf).
+ * psi    : (B,W,C) fp64 out: log p_ctc(g.c, ...); psi[...,blank] = -inf.   psi_eos (B,W) = log p_ctc(g) (optional).
  * mdd_prefix_advance recomputes and stores the state of the chosen (parent hypothesis, label) pairs:
- * sel_hyp, sel_label int32 (B,W) -> r_new (B,W,T,2).
+ * sel_hyp, sel_label int32 (B,W) -> r_new (B,W,T,2); slots with skip_new != 0 or sel_hyp < 0 are left untouched.
+ * mdd_prefix_select is the beam step between the two (nearest reference code: the sort + [:beamWidth] of
+ * BeamSearch.py:52-57): per utterance, over all W*C candidates,
+ *     value(w,c) = score[w] + ctc_weight * (psi[w,c] - psi_prev[w]) + (1 - ctc_weight) * att[w,c]     (c != blank)
+ * with c == eos scored by psi_eos[w], finished hypotheses carried unchanged, NaN and -inf excluded; the W best
+ * (ties: smaller w*C + c) become the new beam: sel_hyp / sel_label (-1 for a dead slot), score_new, psi_new, glen_new,
+ * finished_new (0 live, 1 finished, 2 dead) and the token histories tokens_new (B,W,max_len) int32 (-1 padded).
+ * eos < 0: no end-of-sequence candidate.  att: (B,W,C) fp32 attention-decoder log-probs.
  * ------------------------------------------------------------------------------------------------------------------ */
 int mdd_prefix_init(const float* x, int T, int B, int C, const int64_t* input_lengths, int blank, int W,
-                    float* r0, mdd_stream_t stream);
+                    double* r0, mdd_stream_t stream);
 int mdd_prefix_score(const float* x, int T, int B, int C, const int64_t* input_lengths, int blank, int W,
-                     const float* r_prev, const int32_t* last, const int32_t* glen, float* psi, float* psi_eos,
-                     mdd_stream_t stream);
+                     const double* r_prev, const int32_t* last, const int32_t* glen, const int32_t* skip, double* psi,
+                     double* psi_eos, mdd_stream_t stream);
 int mdd_prefix_advance(const float* x, int T, int B, int C, const int64_t* input_lengths, int blank, int W,
-                       const float* r_prev, const int32_t* last, const int32_t* glen, const int32_t* sel_hyp,
-                       const int32_t* sel_label, float* r_new, mdd_stream_t stream);
+                       const double* r_prev, const int32_t* last, const int32_t* glen, const int32_t* sel_hyp,
+                       const int32_t* sel_label, const int32_t* skip_new, double* r_new, mdd_stream_t stream);
+int mdd_prefix_select(int B, int W, int C, int blank, int eos, double ctc_weight, int max_len, const double* psi,
+                      const double* psi_eos, const float* att, const double* score, const double* psi_prev,
+                      const int32_t* glen, const int32_t* finished, const int32_t* tokens, int32_t* sel_hyp,
+                      int32_t* sel_label, double* score_new, double* psi_new, int32_t* glen_new, int32_t* finished_new,
+                      int32_t* tokens_new, mdd_stream_t stream);
 
 #ifdef __cplusplus
 }

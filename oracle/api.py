@@ -310,3 +310,37 @@ def prefix_score(x, r_prev, last, glen, blank=0):
     lib().orc_prefix_score(_p(x, C.c_double), T, Cc, blank, _p(r_prev, C.c_double), int(last), int(glen),
                            _p(psi, C.c_double), _p(r, C.c_double), C.byref(eos))
     return psi, r, float(eos.value)
+
+
+def joint_beam_search(x, lens, att_fn, beam=10, ctc_weight=0.3, max_len=None, blank=0, eos=None):
+    """fp64 restatement of mddctc.prefix.joint_beam_search: x (T,B,C) log-probs, lens[B],
+    att_fn(step, state) -> (B,W,C) float32 attention log-probs; state = dict of numpy arrays (tokens, last, glen, flag).
+    Returns (tokens[B,W,max_len] int32, scores[B,W] fp64, glen[B,W], flag[B,W])."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    T, B, Cc = x.shape
+    W = beam
+    max_len = max_len or T
+    lens = np.ascontiguousarray(lens, dtype=np.int64)
+    r = np.full((B, W, T, 2), -np.inf, dtype=np.float64)
+    for b in range(B):
+        r0 = prefix_init(x[:lens[b], b], blank)
+        r[b, :, :lens[b]] = r0[None]
+    last = np.full((B, W), -1, dtype=np.int32)
+    glen = np.zeros((B, W), dtype=np.int32)
+    psi = np.zeros((B, W), dtype=np.float64)
+    score = np.full((B, W), -np.inf, dtype=np.float64)
+    flag = np.full((B, W), 2, dtype=np.int32)
+    score[:, 0] = 0.0
+    flag[:, 0] = 0
+    tokens = np.full((B, W, max_len), -1, dtype=np.int32)
+    for step in range(max_len):
+        att = np.ascontiguousarray(att_fn(step, {"tokens": tokens, "last": last, "glen": glen, "flag": flag}),
+                                   dtype=np.float32)
+        assert att.shape == (B, W, Cc)
+        rc = lib().orc_joint_step(_p(x, C.c_double), T, B, Cc, _p(lens, C.c_int64), blank, -1 if eos is None else eos,
+                                  W, C.c_double(ctc_weight), max_len, _p(att, C.c_float), _p(r, C.c_double),
+                                  _p(last, C.c_int32), _p(glen, C.c_int32), _p(psi, C.c_double), _p(score, C.c_double),
+                                  _p(flag, C.c_int32), _p(tokens, C.c_int32))
+        if rc:
+            raise RuntimeError("orc_joint_step failed")
+    return tokens, score, glen, flag

@@ -568,3 +568,111 @@ ORC_API int orc_prefix_score(const double* x, int Tb, int C, int blank, const do
     if (psi_eos) *psi_eos = Tb > 0 ? orc_lse2d(r_prev[2 * (Tb - 1)], r_prev[2 * (Tb - 1) + 1]) : -INFINITY;
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * 7. One step of the label-synchronous joint CTC/attention beam search (not in the
+ *    reference -- nearest code: the sort + [:beamWidth] of BeamSearch.py:52-57 around the recursion above).
+ *    Per utterance, over the W hypothesis slots and C labels:
+ *      value(w,c) = score[w] + lam * (psi(g_w.c) - psi(g_w)) + (1 - lam) * att[w,c]       c != blank
+ *    c == eos is scored with psi_eos(g_w); a finished slot (flag 1) is carried unchanged as its (w, eos) candidate;
+ *    dead slots (flag 2) and -inf / NaN values yield nothing.  The W best (ties: smaller w*C + c) form the new
+ *    beam; a slot without a candidate is dead.  State per slot: r (T,2), last, glen, psi, score, flag,
+ *    tokens (max_len, -1 padded).  x: (T,B,C) fp64, lens[B]; all state arrays are (B,W,...) and are updated in place.
+ * ---------------------------------------------------------------------------------------------- */
+#include <pthread.h>
+struct orc_joint_args {
+    const double* x; int T, B, C; const int64_t* lens; int blank, eos, W; double lam; int max_len; const float* att;
+    double* r; int32_t* last; int32_t* glen; double* psi_st; double* score; int32_t* flag; int32_t* tokens;
+    int first, stride, rc;
+};
+static void* orc_joint_worker(void* vp) {
+    struct orc_joint_args* a = (struct orc_joint_args*)vp;
+    const double* x = a->x; const int T = a->T, B = a->B, C = a->C, blank = a->blank, eos = a->eos, W = a->W;
+    const int max_len = a->max_len; const double lam = a->lam; const float* att = a->att; const int64_t* lens = a->lens;
+    double* r = a->r; int32_t* last = a->last; int32_t* glen = a->glen; double* psi_st = a->psi_st;
+    double* score = a->score; int32_t* flag = a->flag; int32_t* tokens = a->tokens;
+    for (int b = a->first; b < B; b += a->stride) {
+        int Tb = lens ? (int)lens[b] : T;
+        if (Tb < 0) Tb = 0;
+        if (Tb > T) Tb = T;
+        double* xb = (double*)malloc(sizeof(double) * (size_t)(Tb > 0 ? Tb : 1) * C);
+        double* psi = (double*)malloc(sizeof(double) * (size_t)W * C);
+        double* pe = (double*)malloc(sizeof(double) * W);
+        double* rall = (double*)malloc(sizeof(double) * (size_t)W * C * (Tb > 0 ? Tb : 1) * 2);
+        double* cand = (double*)malloc(sizeof(double) * (size_t)W * C);
+        double* r_new = (double*)malloc(sizeof(double) * (size_t)W * T * 2);
+        int32_t* tok_new = (int32_t*)malloc(sizeof(int32_t) * (size_t)W * max_len);
+        int32_t n_last[64], n_glen[64], n_flag[64];
+        double n_psi[64], n_score[64];
+        if (!xb || !psi || !pe || !rall || !cand || !r_new || !tok_new || W > 64) { a->rc = -1; goto done; }
+        for (int t = 0; t < Tb; ++t) memcpy(xb + (size_t)t * C, x + ((size_t)t * B + b) * C, sizeof(double) * C);
+        for (int w = 0; w < W; ++w) {
+            const int s = b * W + w;
+            for (int c = 0; c < C; ++c) cand[w * C + c] = -INFINITY;
+            if (flag[s] == 1) { cand[w * C + (eos >= 0 ? eos : blank)] = score[s]; continue; }
+            if (flag[s] != 0 || !(score[s] > -INFINITY)) continue;
+            /* the slot's r lives at stride T in the state; orc_prefix_score wants (Tb,2): the first Tb rows */
+            orc_prefix_score(xb, Tb, C, blank, r + (size_t)s * T * 2, last[s], glen[s], psi + (size_t)w * C,
+                             rall + (size_t)w * C * Tb * 2, &pe[w]);
+            for (int c = 0; c < C; ++c) {
+                if (c == blank) continue;
+                const double pc = (c == eos) ? pe[w] : psi[w * C + c];
+                double v = -INFINITY;
+                if (pc > -INFINITY && psi_st[s] > -INFINITY)
+                    v = score[s] + lam * (pc - psi_st[s]) + (1.0 - lam) * (double)att[(size_t)s * C + c];
+                if (v != v) v = -INFINITY;
+                cand[w * C + c] = v;
+            }
+        }
+        for (int k = 0; k < W; ++k) {
+            int bi = -1;
+            double bv = -INFINITY;
+            for (int i = 0; i < W * C; ++i)
+                if (cand[i] > bv) { bv = cand[i]; bi = i; }
+            int32_t* tk = tok_new + (size_t)k * max_len;
+            if (bi < 0) {
+                n_last[k] = -1; n_glen[k] = 0; n_flag[k] = 2; n_psi[k] = -INFINITY; n_score[k] = -INFINITY;
+                for (int i = 0; i < max_len; ++i) tk[i] = -1;
+                continue;
+            }
+            const int w = bi / C, c = bi % C, s = b * W + w;
+            const int pf = flag[s] != 0;
+            cand[bi] = -INFINITY;
+            n_last[k] = c;
+            n_glen[k] = glen[s] + (pf ? 0 : 1);
+            n_flag[k] = (pf || c == eos) ? 1 : 0;
+            n_score[k] = bv;
+            n_psi[k] = pf ? psi_st[s] : (c == eos ? pe[w] : psi[w * C + c]);
+            memcpy(tk, tokens + (size_t)s * max_len, sizeof(int32_t) * max_len);
+            if (!pf && glen[s] < max_len) tk[glen[s]] = c;
+            double* rn = r_new + (size_t)k * T * 2;
+            for (int t = 0; t < 2 * T; ++t) rn[t] = -INFINITY;
+            if (!n_flag[k]) memcpy(rn, rall + ((size_t)w * C + c) * Tb * 2, sizeof(double) * Tb * 2);
+        }
+        for (int k = 0; k < W; ++k) {
+            const int s = b * W + k;
+            last[s] = n_last[k]; glen[s] = n_glen[k]; flag[s] = n_flag[k]; psi_st[s] = n_psi[k]; score[s] = n_score[k];
+        }
+        memcpy(r + (size_t)b * W * T * 2, r_new, sizeof(double) * (size_t)W * T * 2);
+        memcpy(tokens + (size_t)b * W * max_len, tok_new, sizeof(int32_t) * (size_t)W * max_len);
+    done:
+        free(xb); free(psi); free(pe); free(rall); free(cand); free(r_new); free(tok_new);
+    }
+    return NULL;
+}
+ORC_API int orc_joint_step(const double* x, int T, int B, int C, const int64_t* lens, int blank, int eos, int W,
+                           double lam, int max_len, const float* att, double* r, int32_t* last, int32_t* glen,
+                           double* psi_st, double* score, int32_t* flag, int32_t* tokens) {
+    enum { NTH = 16 };
+    pthread_t th[NTH];
+    struct orc_joint_args args[NTH];
+    int n = B < NTH ? B : NTH, rc = 0;
+    for (int i = 0; i < n; ++i) {
+        struct orc_joint_args a = {x, T, B, C, lens, blank, eos, W, lam, max_len, att, r, last, glen, psi_st, score, flag,
+                                   tokens, i, n, 0};
+        args[i] = a;
+        if (pthread_create(&th[i], NULL, orc_joint_worker, &args[i]) != 0) { orc_joint_worker(&args[i]); th[i] = 0; }
+    }
+    for (int i = 0; i < n; ++i) { if (th[i]) pthread_join(th[i], NULL); if (args[i].rc) rc = args[i].rc; }
+    return rc;
+}

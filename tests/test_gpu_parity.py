@@ -132,7 +132,7 @@ def _aligned_logits(T, B, C, L, il, tl, tg, boost, noise, g):
 
 
 ENVELOPE = [  # name, boost (None = unstructured randn * scale), noise / scale, the first pass keeps everything, the
-    # second tier (2-frame chunks over the flagged list) leaves nothing for the log-space kernel
+    # second tier (2-frame chunks over the flagged list) leaves nothing for the fp64 kernel
     ("randn*2", None, 2.0, True, True), ("randn*3", None, 3.0, False, True), ("randn*5", None, 5.0, False, False),
     ("aligned+6", 6, 0.1, True, True), ("aligned+10", 10, 0.1, True, True), ("aligned+10 clean", 10, 0.0, True, True),
     ("aligned+16", 16, 0.1, False, True), ("aligned+25", 25, 0.1, False, False),
@@ -142,10 +142,11 @@ ENVELOPE = [  # name, boost (None = unstructured randn * scale), noise / scale, 
 
 @pytest.mark.parametrize("name,boost,par,all_fast,no_log", ENVELOPE, ids=[e[0] for e in ENVELOPE])
 def test_ctc_packed_kernel_envelope(M, name, boost, par, all_fast, no_log):
-    """The packed linear-domain kernel has a finite dynamic range (block floating point, one exponent per lane and
-    chunk).  Whatever it does not hand to the log-space kernel must be RIGHT: on peaky 'trained model' posteriors, with
-    and without confidently wrong frames, every utterance it keeps agrees with the log-space kernel and a sample agrees
-    with torch CPU fp64; on the benign families it keeps all of them (no 4 ms fallback for ordinary inputs)."""
+    """The packed fp32 kernel has a finite dynamic range (block floating point, one exponent per lane and chunk).
+    Whatever it does not hand on must be RIGHT, and whatever it hands on is redone by the fp64 kernel: on peaky
+    'trained model' posteriors, with and without confidently wrong frames, EVERY utterance of the product path --
+    whichever tier produced it -- holds north_star's tolerance against torch CPU fp64; on the benign families the first
+    pass keeps all of them."""
     from mddctc.loss import ctc_loss_raw, last_fallback_flags
     g = torch.Generator(device="cuda").manual_seed(21)
     T, B, C, L = 600, 256, 42, 80
@@ -157,30 +158,67 @@ def test_ctc_packed_kernel_envelope(M, name, boost, par, all_fast, no_log):
     else:
         x = _aligned_logits(T, B, C, L, il, tl, tg, boost, par, g)
     lp = torch.log_softmax(x, -1)
-    n1, g1, _ = ctc_loss_raw(lp, tg, il, tl, algo=1)
-    n1, g1 = n1.clone(), g1.clone()
-    n2, g2, _ = ctc_loss_raw(lp, tg, il, tl, algo=2, validate=False)          # packed kernel alone, no fallback
+    ref_nll, ref_grad = _torch_cpu_ctc(lp, tg, il, tl, dtype=torch.float64)   # the truth, all B utterances
+    ref_nll, ref_grad = ref_nll.cuda(), ref_grad.cuda()
+
+    def err(n, gr, mask=None):
+        ne = ((n.double() - ref_nll) / ref_nll).abs()
+        ge = (gr.double() - ref_grad).abs().amax(dim=(0, 2))
+        if mask is not None:
+            ne, ge = ne[mask], ge[mask]
+        return (float(ne.max()), float(ge.max())) if ne.numel() else (0.0, 0.0)
+
+    n1, g1, _ = ctc_loss_raw(lp, tg, il, tl, algo=1)                          # the fp64 kernel: exact to fp32 rounding
+    e1 = err(n1, g1)
+    assert e1[0] < 1e-6 and e1[1] < 2e-6, (name, e1)
+    n2, g2, _ = ctc_loss_raw(lp, tg, il, tl, algo=2, validate=False)          # first packed pass alone, no fallback
     kept = last_fallback_flags(B) == 0
     if all_fast:
         assert bool(kept.all()), (name, (~kept).nonzero().flatten()[:8].tolist())
-    assert float(((n1 - n2) / n1).abs()[kept].max()) < LOSS_RTOL if kept.any() else True
-    # the log-space kernel itself is good to ~2.5e-4 on high-loss inputs (fp32 log domain), hence the 4e-4
-    assert float((g1 - g2).abs().amax(dim=(0, 2))[kept].max()) < 4e-4 if kept.any() else True
-    n0, g0, _ = ctc_loss_raw(lp, tg, il, tl, algo=0)                          # the product path, against fp64
+    e2 = err(n2, g2, kept)                                                    # what it keeps is right
+    assert e2[0] < LOSS_RTOL and e2[1] <= GRAD_ATOL, (name, e2)
+    n0, g0, _ = ctc_loss_raw(lp, tg, il, tl, algo=0)                          # the product path
     n0, g0 = n0.clone(), g0.clone()
-    n0b, g0b, _ = ctc_loss_raw(lp, tg, il, tl, algo=0)                        # ... which is bitwise reproducible,
-    assert torch.equal(n0, n0b) and torch.equal(g0, g0b, ) or bool(torch.isnan(g0).any())    # whichever tiers ran
+    n0b, g0b, _ = ctc_loss_raw(lp, tg, il, tl, algo=0)                        # ... is bitwise reproducible,
+    assert torch.equal(n0, n0b) and torch.equal(g0, g0b)                      # whichever tiers ran
     left = last_fallback_flags(B) != 0                                        # what the two packed tiers did not finish
     if no_log:                                                                # a stray utterance (< 2 %) may still go on
         assert int(left.sum()) <= (0 if all_fast else B // 50), (name, left.nonzero().flatten()[:8].tolist())
-    # every utterance, whichever tier produced it, agrees with the log-space kernel
-    assert float(((n1 - n0) / n1).abs().max()) < LOSS_RTOL
-    assert float((g1 - g0).abs().max()) < 4e-4
-    sel = torch.arange(0, B, B // 6)[:6]
-    ref_nll, ref_grad = _torch_cpu_ctc(lp[:, sel], tg[sel], il[sel], tl[sel], dtype=torch.float64)
-    np.testing.assert_allclose(n0[sel].cpu().numpy(), ref_nll.numpy(), rtol=LOSS_RTOL)
-    tol = GRAD_ATOL if all_fast else 4e-4
-    assert float((g0[:, sel].cpu().double() - ref_grad).abs().max()) <= tol
+    e0 = err(n0, g0)
+    print("envelope %-20s first pass kept %d/%d, left for fp64 %d | loss rel %.2e grad abs %.2e (fp64 kernel %.1e)"
+          % (name, int(kept.sum()), B, int(left.sum()), e0[0], e0[1], e1[1]))
+    assert e0[0] < LOSS_RTOL and e0[1] <= GRAD_ATOL, (name, e0)
+
+
+@pytest.mark.parametrize("seed", [3, 4, 5])
+def test_ctc_long_ragged_t1500(M, seed):
+    """BASELINE config 5's length range: T ragged 50..1500, L up to 180, log_softmax(randn) and a peaky family;
+    loss 1e-5 relative, gradient 1e-4 absolute against torch CPU fp64 on every utterance, margin reported."""
+    from mddctc.loss import ctc_loss_raw, last_fallback_flags
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    T, B, C, L = 1500, 96, 42, 180
+    il = torch.randint(50, T + 1, (B,), generator=g, device="cuda")
+    il[:8] = T                                                                # the longest case is always present
+    tl = torch.minimum(torch.randint(1, L + 1, (B,), generator=g, device="cuda"), (il // 3).clamp(min=1))
+    tl[:8] = L
+    tg = torch.randint(1, C, (B, L), generator=g, device="cuda")
+    worst = 0.0
+    for fam in ("randn", "aligned+12"):
+        if fam == "randn":
+            x = torch.randn(T, B, C, generator=g, device="cuda")
+        else:
+            x = _aligned_logits(T, B, C, L, il, tl, tg, 12, 0.1, g)
+        lp = torch.log_softmax(x, -1)
+        ref_nll, ref_grad = _torch_cpu_ctc(lp, tg, il, tl, dtype=torch.float64)
+        for algo in (0, 1):
+            nll, grad, _ = ctc_loss_raw(lp, tg, il, tl, algo=algo)
+            np.testing.assert_allclose(nll.cpu().numpy(), ref_nll.numpy(), rtol=LOSS_RTOL)
+            ge = float((grad.cpu().double() - ref_grad).abs().max())
+            if algo == 0:
+                worst = max(worst, ge)
+                assert int((last_fallback_flags(B) != 0).sum()) == 0, fam    # the packed kernel produced all of them
+            assert ge <= (GRAD_ATOL if algo == 0 else 2e-6), (fam, algo, ge)
+    print("T=1500 ragged seed %d: worst gradient error of the packed path %.2e (bound %.0e)" % (seed, worst, GRAD_ATOL))
 
 
 # ------------------------------------------------------------------------------- CTC from logits (SURVEY 8f rank 1)
@@ -786,7 +824,7 @@ def test_prefix_scorer_vs_oracle_and_invariant(M):
     scorer = CTCPrefixScorer(x.cuda(), lens.cuda(), blank=0, beam=W)
     labels = [[1, 2, 2, 5, 7], [3, 3, 3], [11, 1]]
     # hypothesis w of utterance b follows labels[b] (rotated by w so that the W hypotheses differ)
-    state = scorer.initial_state()
+    state = scorer.initial_state(all_slots_live=True)
     seqs = [[list(np.roll(labels[b], w)) for w in range(W)] for b in range(B)]
     nsteps = max(len(s) for s in labels)
     r_or = [[O.prefix_init(x[:lens[b], b].double().numpy()) for w in range(W)] for b in range(B)]
@@ -794,7 +832,6 @@ def test_prefix_scorer_vs_oracle_and_invariant(M):
     for n in range(nsteps):
         psi, eos = scorer.score(state)
         psi, eos = psi.cpu().numpy(), eos.cpu().numpy()
-        sel_h = torch.zeros((B, W), dtype=torch.int32)
         sel_l = torch.zeros((B, W), dtype=torch.int32)
         for b in range(B):
             for w in range(W):
@@ -802,21 +839,63 @@ def test_prefix_scorer_vs_oracle_and_invariant(M):
                 want_psi, want_r, want_eos = O.prefix_score(x[:lens[b], b].double().numpy(), r_or[b][w], last[b][w], glen)
                 fin = np.isfinite(want_psi)
                 assert np.array_equal(np.isfinite(psi[b, w]), fin)
-                np.testing.assert_allclose(psi[b, w][fin], want_psi[fin], rtol=1e-5, atol=1e-5)
-                np.testing.assert_allclose(eos[b, w], want_eos, rtol=1e-5, atol=1e-5)
+                np.testing.assert_allclose(psi[b, w][fin], want_psi[fin], rtol=1e-12, atol=1e-12)   # fp64 on both sides
+                np.testing.assert_allclose(eos[b, w], want_eos, rtol=1e-12, atol=1e-12)
                 c = seqs[b][w][n] if n < len(seqs[b][w]) else None
-                sel_h[b, w] = w
                 sel_l[b, w] = c if c is not None else -1
                 if c is not None:
                     r_or[b][w], last[b][w] = want_r[c], c
-        # hypotheses that are finished keep their state (label -1 is reported as invalid -> state of -inf, unused after)
-        keep = sel_l >= 0
-        state = scorer.advance(state, sel_h.cuda(), sel_l.cuda(), keep.cuda())
+        state = scorer.extend(state, sel_l.cuda())         # label -1: the slot keeps its state
     psi, eos = scorer.score(state)
     for b in range(B):
         nll = torch.nn.functional.ctc_loss(x[:, b:b + 1].double(), torch.tensor([labels[b]]), lens[b:b + 1],
                                            torch.tensor([len(labels[b])]), reduction="none")
-        assert abs(float(eos[b, 0]) + float(nll)) < 1e-4 * max(1.0, abs(float(nll)))
+        assert abs(float(eos[b, 0]) + float(nll)) < 1e-10 * max(1.0, abs(float(nll)))
+
+
+def _synthetic_attention(C, periods=7, seed=0):
+    """A stand-in attention decoder (the reference has none): log-probs that depend on the decoding step and on the
+    hypothesis' last label, att[b,w,:] = table[step % periods, last + 1]; identical on both sides of a parity test."""
+    g = torch.Generator().manual_seed(seed)
+    return torch.log_softmax(torch.randn(periods, C + 1, C, generator=g) * 2.0, -1)
+
+
+@pytest.mark.parametrize("eos", [None, 42])
+def test_joint_beam_search_config4_vs_oracle(M, eos):
+    """BASELINE config 4 shape (beam 10, CTC weight 0.3, T = 500, C = 43) on 64 utterances: the whole joint beam search
+    (prefix scorer + in-library top-W selection + state advance) against the fp64 CPU restatement of the same loop:
+    tokens, lengths and flags identical, scores to 1e-9."""
+    from mddctc.prefix import joint_beam_search
+    g = torch.Generator().manual_seed(44)
+    T, B, C, W, steps = 500, 64, 43, 10, 24
+    xl = torch.randn(T, B, C, generator=g)
+    xl[:, :, 0] += 3.0
+    pk = torch.randint(1, C - 1, (T, B), generator=g)
+    xl.scatter_add_(2, pk[..., None], 4.0 * (torch.rand(T, B, 1, generator=g) < 0.3).float())
+    x = torch.log_softmax(xl, -1)
+    lens = torch.randint(300, T + 1, (B,), generator=g)
+    lens[0], lens[1] = T, 14                                     # a full-length one and one shorter than the search
+    table = _synthetic_attention(C)
+    tab_d = table.cuda()
+
+    def att_dev(step, st):
+        return tab_d[step % tab_d.shape[0]][(st["last"] + 1).long()]
+
+    def att_cpu(step, st):
+        return table[step % table.shape[0]][torch.from_numpy(st["last"] + 1).long()].numpy()
+
+    tok, sc, gl, fl = joint_beam_search(x.cuda(), lens.cuda(), att_dev, beam=W, ctc_weight=0.3, max_len=steps, eos=eos)
+    wt, ws, wg, wf = O.joint_beam_search(x.numpy(), lens.numpy(), att_cpu, beam=W, ctc_weight=0.3, max_len=steps, eos=eos)
+    assert np.array_equal(fl.cpu().numpy(), wf)
+    assert np.array_equal(gl.cpu().numpy(), wg)
+    assert np.array_equal(tok.cpu().numpy(), wt)
+    got = sc.cpu().numpy()
+    fin = np.isfinite(ws)
+    assert np.array_equal(np.isfinite(got), fin)
+    np.testing.assert_allclose(got[fin], ws[fin], rtol=1e-9, atol=1e-9)
+    assert bool((np.diff(np.where(fin, ws, -1e300), axis=1) <= 0).all())          # best first
+    if eos is not None:
+        assert int((wf == 1).sum()) > 0                                          # some hypotheses did end
 
 
 # ----------------------------------------------------------------------------------------------------- corpus MDD evaluation

@@ -220,3 +220,48 @@ def test_corpus_insertion_keys_unique():
     """print_align_space_canonical_origin keys an insertion by str(j-1)+str(j) (:61); the oracle stores j."""
     keys = [str(j - 1) + str(j) for j in range(0, 5000)]
     assert len(set(keys)) == len(keys)
+
+
+def test_joint_beam_step_c_vs_python_restatement():
+    """The C restatement of the joint CTC/attention beam step (orc_joint_step; SURVEY Appendix A.6, reference-unpinned)
+    against an independent pure-Python loop over O.prefix_score: same tokens, scores, flags, with and without eos,
+    including hypotheses that die because the utterance is shorter than the search."""
+    rng = np.random.default_rng(0)
+    T, B, C, W, steps = 14, 3, 6, 3, 5
+    x = np.log(rng.dirichlet(np.ones(C), (T, B)))
+    lens = np.array([14, 9, 4])
+    tab = np.log(rng.dirichlet(np.ones(C), (4, C + 1))).astype(np.float32)
+
+    def att(step, st):
+        return tab[step % 4][st["last"] + 1]
+
+    for eos in (None, 5):
+        tok, sc, gl, fl = O.joint_beam_search(x, lens, att, beam=W, ctc_weight=0.3, max_len=steps, eos=eos)
+        for b in range(B):
+            xb = x[:lens[b], b]
+            hyps = [dict(r=O.prefix_init(xb), last=-1, glen=0, psi=0.0, score=0.0, flag=0, tok=[])]
+            for step in range(steps):
+                cands = []
+                for w, h in enumerate(hyps):
+                    if h["flag"] == 1:
+                        cands.append((h["score"], w, eos, h, None))
+                        continue
+                    psi, r, pe = O.prefix_score(xb, h["r"], h["last"], h["glen"])
+                    a = tab[step % 4][h["last"] + 1]
+                    for c in range(1, C):
+                        pc = pe if c == eos else psi[c]
+                        if np.isfinite(pc):
+                            cands.append((h["score"] + 0.3 * (pc - h["psi"]) + 0.7 * float(a[c]), w, c, h, (r[c], pc)))
+                cands.sort(key=lambda z: (-z[0], z[1] * C + z[2]))
+                new = []
+                for v, w, c, h, ex in cands[:W]:
+                    if h["flag"] == 1:
+                        new.append(h)
+                    else:
+                        new.append(dict(r=ex[0], last=c, glen=h["glen"] + 1, psi=ex[1], score=v,
+                                        flag=1 if c == eos else 0, tok=h["tok"] + [c]))
+                hyps = new
+            for k, h in enumerate(hyps):
+                assert list(tok[b, k, :len(h["tok"])]) == h["tok"]
+                assert abs(sc[b, k] - h["score"]) < 1e-9 and fl[b, k] == h["flag"] and gl[b, k] == len(h["tok"])
+            assert all(fl[b, k] == 2 for k in range(len(hyps), W))
