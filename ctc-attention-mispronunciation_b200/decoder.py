@@ -133,37 +133,6 @@ class Decoder(object):
         return r[0] if isinstance(r, tuple) else r
 
     # ---------------------------------------------------------------------------------------------- string helpers
-    def _unflatten_targets(self, targets, target_sizes):
-        split_targets, offset = [], 0
-        for size in target_sizes:
-            split_targets.append(targets[offset: offset + size])
-            offset += size
-        return split_targets
-
-    def _process_strings(self, seqs, remove_rep=False):
-        return [self._process_string(seq, remove_rep) for seq in seqs]
-
-    def _process_string(self, seq, remove_rep=False):
-        string = ""
-        for i, char in enumerate(seq):
-            if char != self.int_to_char[self.blank_index]:
-                if remove_rep and i != 0 and char == seq[i - 1]:
-                    pass
-                elif self.space_idx == -1:
-                    string = string + " " + char
-                elif char == self.int_to_char[self.space_idx]:
-                    string += " "
-                else:
-                    string = string + char
-        return string
-
-    def _convert_to_strings(self, seq, sizes=None):
-        return [self._convert_to_string(seq[x], sizes[x] if sizes is not None else len(seq[x])) for x in range(len(seq))]
-
-    def _convert_to_string(self, seq, sizes):
-        result = [self.int_to_char[seq[i]] for i in range(sizes)]
-        return result if self.space_idx == -1 else "".join(result)
-
     def _word_ids(self, n_class):
         """int32[C]: equal ids <=> equal word strings (the repeat rule compares strings, ctcDecoder.py:83-84)."""
         seen, out = {}, np.zeros(n_class, dtype=np.int32)

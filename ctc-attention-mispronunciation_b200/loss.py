@@ -105,41 +105,64 @@ def ctc_loss_raw(log_probs, targets, input_lengths, target_lengths, blank=0, zer
 def ctc_loss_streamed(log_probs_host, targets, input_lengths, target_lengths, slices=4, blank=0, zero_infinity=False,
                       grad_scalar=1.0, staging=None, algo=0):
     """CTC loss + gradient of a batch whose log-probs live in (page-locked) HOST memory, as the reference keeps them for
-    decoding (infer.py:300): the batch is cut into `slices` contiguous batch slices; slice k+1 crosses PCIe
-    (mdd_copy_h2d_2d on a side stream) while the kernels of slice k run.  Targets and lengths are device tensors.
+    decoding (infer.py:300): slice k+1 of the batch crosses PCIe on a side stream while the kernels of slice k run.
+    Targets and lengths are device tensors.
 
-    Returns (loss_sum [1] device, nll [B] device, [grad slices (T, B_k, C)]); `staging` is an optional (T,B,C) device
-    buffer to receive the log-probs (kept by the caller between steps)."""
+    ``log_probs_host`` is either
+      * a LIST of contiguous fp32 (T, B_k, C) host tensors -- slice-major, the layout a producer that emits the batch in
+        micro-batches has anyway: every transfer is ONE contiguous copy; or
+      * one contiguous fp32 (T, B, C) host tensor, cut into `slices` batch slices (each transfer is then a strided 2-D
+        copy of T rows, mdd_copy_h2d_2d).
+    Returns (loss_sum [1] device, nll [B] device, [grad slices (T, B_k, C)]); `staging` optionally holds the device
+    buffers that receive the log-probs between steps (a (T,B,C) tensor for the single-tensor form, a list of
+    (T,B_k,C) tensors for the list form)."""
     L = _lib.lib()
-    if log_probs_host.is_cuda or log_probs_host.dim() != 3 or log_probs_host.dtype != torch.float32 \
-            or not log_probs_host.is_contiguous():
-        raise RuntimeError("ctc_loss_streamed takes a contiguous fp32 (T,B,C) host tensor")
     dev = _rt.device(targets)
-    T, B, C = log_probs_host.shape
-    lp_d = torch.empty((T, B, C), dtype=torch.float32, device=dev) if staging is None else staging
     cur, side = torch.cuda.current_stream(dev), _rt.copy_stream(dev)
-    side.wait_stream(cur)                                   # the staging buffer may still be read by earlier kernels
-    slices = max(1, min(int(slices), B))
-    base, rem = divmod(B, slices)
-    bounds, lo = [], 0
-    for k in range(slices):
-        hi = lo + base + (1 if k < rem else 0)
-        bounds.append((lo, hi))
-        lo = hi
-    pitch = B * C * 4
-    events = []
-    for lo, hi in bounds:
-        _lib.check(L.mdd_copy_h2d_2d(lp_d.data_ptr() + lo * C * 4, pitch, log_probs_host.data_ptr() + lo * C * 4, pitch,
-                                     (hi - lo) * C * 4, T, side.cuda_stream), "mdd_copy_h2d_2d")
-        ev = torch.cuda.Event()
-        ev.record(side)
-        events.append(ev)
-    parts = torch.zeros(slices, dtype=torch.float32, device=dev)
+    side.wait_stream(cur)                                   # the staging buffers may still be read by earlier kernels
+    events, views, bounds = [], [], []
+    if isinstance(log_probs_host, (list, tuple)):
+        lo = 0
+        for k, h in enumerate(log_probs_host):
+            if h.is_cuda or h.dim() != 3 or h.dtype != torch.float32 or not h.is_contiguous():
+                raise RuntimeError("ctc_loss_streamed takes contiguous fp32 (T,B_k,C) host tensors")
+            d = staging[k] if staging is not None else torch.empty(h.shape, dtype=torch.float32, device=dev)
+            with torch.cuda.stream(side):
+                d.copy_(h, non_blocking=True)               # one contiguous cudaMemcpyAsync
+            ev = torch.cuda.Event()
+            ev.record(side)
+            events.append(ev)
+            views.append(d)
+            bounds.append((lo, lo + h.shape[1]))
+            lo += h.shape[1]
+        B = lo
+    else:
+        if log_probs_host.is_cuda or log_probs_host.dim() != 3 or log_probs_host.dtype != torch.float32 \
+                or not log_probs_host.is_contiguous():
+            raise RuntimeError("ctc_loss_streamed takes a contiguous fp32 (T,B,C) host tensor")
+        T, B, C = log_probs_host.shape
+        lp_d = torch.empty((T, B, C), dtype=torch.float32, device=dev) if staging is None else staging
+        slices = max(1, min(int(slices), B))
+        base, rem = divmod(B, slices)
+        lo = 0
+        for k in range(slices):
+            hi = lo + base + (1 if k < rem else 0)
+            bounds.append((lo, hi))
+            lo = hi
+        pitch = B * C * 4
+        for lo, hi in bounds:
+            _lib.check(L.mdd_copy_h2d_2d(lp_d.data_ptr() + lo * C * 4, pitch, log_probs_host.data_ptr() + lo * C * 4,
+                                         pitch, (hi - lo) * C * 4, T, side.cuda_stream), "mdd_copy_h2d_2d")
+            ev = torch.cuda.Event()
+            ev.record(side)
+            events.append(ev)
+            views.append(lp_d[:, lo:hi])
+    parts = torch.zeros(len(bounds), dtype=torch.float32, device=dev)
     nll = torch.empty(B, dtype=torch.float32, device=dev)
     grads = []
     for k, (lo, hi) in enumerate(bounds):
         cur.wait_event(events[k])
-        _, g, _ = ctc_loss_raw(lp_d[:, lo:hi], targets[lo:hi], input_lengths[lo:hi], target_lengths[lo:hi], blank=blank,
+        _, g, _ = ctc_loss_raw(views[k], targets[lo:hi], input_lengths[lo:hi], target_lengths[lo:hi], blank=blank,
                                zero_infinity=zero_infinity, grad_scalar=grad_scalar, algo=algo, validate=False,
                                loss_sum=parts[k:k + 1], nll=nll[lo:hi])
         grads.append(g)
@@ -149,7 +172,7 @@ def ctc_loss_streamed(log_probs_host, targets, input_lengths, target_lengths, sl
 def last_fallback_flags(B, dev=None):
     """Diagnostics: the per-utterance flags the last mdd_ctc_loss call on this device left in its workspace
     (0 = the packed linear-domain kernel produced the result -- in its first pass or, with algo=0, in its second tier at
-    2 frames per chunk -- otherwise the log-space kernel redid the utterance; after an algo=2 call: what the first pass
+    2 frames per chunk -- otherwise the fp64 kernel redid the utterance; after an algo=2 call: what the first pass
     alone handed on)."""
     dev = _rt.device() if dev is None else dev
     ws = _rt._ws_cache[(dev.index, "ctc")]
