@@ -105,6 +105,8 @@ int ctc_loss_impl(const float* log_probs, int T, int B, int C, int64_t stride_t,
         if (rc) return rc;
     }
     int kern = T > 0 ? ctc_kernel_choice(C, max_target_len, algo) : 0;
+    // the packed kernel addresses rows with 32-bit byte pitches
+    if (kern && (stride_t * 4 >= (1ll << 32) || (int64_t)B * C * 4 >= (1ll << 32) || stride_t < 0 || stride_b < 0)) kern = 0;
     if (algo == 2 && kern != 1) return MDD_E_UNSUPPORTED;
     if (row_lse) {
         rc = launch_row_lse(log_probs, T, B, C, stride_t, stride_b, row_lse, argmax, st);

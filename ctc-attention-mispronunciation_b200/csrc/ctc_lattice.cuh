@@ -133,38 +133,48 @@ template <int NSL>
 __device__ __forceinline__ void renorm_alpha(float2 (&a)[NSL], int (&ea)[2], float2& sca, int lane, bool (&ok)[2],
                                              bool strict = false, int decay_max = 1 << 20) {
     constexpr int GAP = PGeo<NSL>::GAP;
-    float f[2], sc[2];
+    // the two utterances side by side: their max-scans are two dependent chains of five shuffles each, and a warp
+    // that runs them one after the other waits out ten shuffle latencies per chunk
+    float m0 = a[0].x, m1 = a[0].y;
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        float m = compc(a[0], h);
-#pragma unroll
-        for (int j = 1; j + 1 < NSL; j += 2) m = fmax3(m, compc(a[j], h), compc(a[j + 1], h));
-        m = fmaxf(m, compc(a[NSL - 1], h));
-        const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;
-        const bool some = m >= 1.17549435e-38f && m < 3.0e38f;       // normal, finite (NaN fails both)
-        const int e_own = some ? ea[h] + k - SHIFT : E_EMPTY;
-        int t = e_own + GAP * lane;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) t = max(t, __shfl_up_sync(FULL, t, d));   // lanes < d get their own value back
-        const int e_new = t - GAP * lane;
-        f[h] = pow2i(ea[h] - e_new);
-        ea[h] = e_new;
-        const int e_nb = __shfl_up_sync(FULL, e_new, 1);
-        sc[h] = lane == 0 ? 0.f : pow2i(e_nb - e_new);
-        // The lanes that hold the bulk of the mass (within 2^64 of the largest) must not have decayed by more than
-        // 2^decay_max since the last renormalisation: beyond that, smaller states of such a lane have been underflowing
-        // inside the chunk, and since the beta exponents are tied to alpha's, the backward sweep is blind to what a
-        // lane lost once the lane's exponent has followed the loss down (the forward/backward check cannot see it).
-        // Lanes far below the bulk decay faster as a matter of course (their paths are the poor ones) and are exempt.
-        const int e_top = __reduce_max_sync(FULL, e_own);
-        const bool fast_decay = some && e_own >= e_top - 64 && k - SHIFT < -decay_max;
-        const bool bad = (m != m) || m >= 3.0e38f || fast_decay || (strict && some && e_new - e_own > 100);
-        ok[h] = __any_sync(FULL, some) && !__any_sync(FULL, bad);
+    for (int j = 1; j + 1 < NSL; j += 2) {
+        m0 = fmax3(m0, a[j].x, a[j + 1].x);
+        m1 = fmax3(m1, a[j].y, a[j + 1].y);
     }
-    const float2 f2 = make_float2(f[0], f[1]);
+    m0 = fmaxf(m0, a[NSL - 1].x);
+    m1 = fmaxf(m1, a[NSL - 1].y);
+    const int k0 = ((__float_as_int(m0) >> 23) & 0xff) - 127, k1 = ((__float_as_int(m1) >> 23) & 0xff) - 127;
+    const bool some0 = m0 >= 1.17549435e-38f && m0 < 3.0e38f;     // normal, finite (NaN fails both)
+    const bool some1 = m1 >= 1.17549435e-38f && m1 < 3.0e38f;
+    const int own0 = some0 ? ea[0] + k0 - SHIFT : E_EMPTY, own1 = some1 ? ea[1] + k1 - SHIFT : E_EMPTY;
+    int t0 = own0 + GAP * lane, t1 = own1 + GAP * lane;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {                            // lanes < d get their own value back
+        const int s0 = __shfl_up_sync(FULL, t0, d), s1 = __shfl_up_sync(FULL, t1, d);
+        t0 = max(t0, s0);
+        t1 = max(t1, s1);
+    }
+    const int new0 = t0 - GAP * lane, new1 = t1 - GAP * lane;
+    const int nb0 = __shfl_up_sync(FULL, new0, 1), nb1 = __shfl_up_sync(FULL, new1, 1);
+    const int top0 = __reduce_max_sync(FULL, own0), top1 = __reduce_max_sync(FULL, own1);
+    // The lanes that hold the bulk of the mass (within 2^64 of the largest) must not have decayed by more than
+    // 2^decay_max since the last renormalisation: beyond that, smaller states of such a lane have been underflowing
+    // inside the chunk, and since the beta exponents are tied to alpha's, the backward sweep is blind to what a
+    // lane lost once the lane's exponent has followed the loss down (the forward/backward check cannot see it).
+    // Lanes far below the bulk decay faster as a matter of course (their paths are the poor ones) and are exempt.
+    const bool fast0 = some0 && own0 >= top0 - 64 && k0 - SHIFT < -decay_max;
+    const bool fast1 = some1 && own1 >= top1 - 64 && k1 - SHIFT < -decay_max;
+    const bool bad0 = (m0 != m0) || m0 >= 3.0e38f || fast0 || (strict && some0 && new0 - own0 > 100);
+    const bool bad1 = (m1 != m1) || m1 >= 3.0e38f || fast1 || (strict && some1 && new1 - own1 > 100);
+    const unsigned bits = __reduce_or_sync(FULL, (some0 ? 1u : 0u) | (bad0 ? 2u : 0u) | (some1 ? 4u : 0u) | (bad1 ? 8u : 0u));
+    ok[0] = (bits & 3u) == 1u;
+    ok[1] = (bits & 12u) == 4u;
+    const float2 f2 = make_float2(pow2i(ea[0] - new0), pow2i(ea[1] - new1));
+    ea[0] = new0;
+    ea[1] = new1;
 #pragma unroll
     for (int j = 0; j < NSL; ++j) a[j] = __fmul2_rn(a[j], f2);
-    sca = make_float2(sc[0], sc[1]);
+    sca = make_float2(lane == 0 ? 0.f : pow2i(nb0 - new0), lane == 0 ? 0.f : pow2i(nb1 - new1));
 }
 
 }  // namespace lattice

@@ -25,8 +25,10 @@
 //  * Class reduction: the product of a label state, as a fixed-point fraction of Z, is added with a shared-memory
 //    integer atomic to the cell of its class, which sits at the class's (bank-coloured) emission position; the lane
 //    that owns the position reads it back.  Integer addition is associative: results are bitwise reproducible.
-//  * Loads that travel far never sit on a register scoreboard next to the lattice's LDS traffic: checkpoints come back
-//    by cp.async, log-prob rows are prefetched into L2 two chunks ahead of their register loads.
+//  * Nothing that travels far touches a register: log-prob rows go global -> shared by cp.async (8-byte pieces, two
+//    chunks ahead, three staging slots), checkpoints likewise one chunk ahead.  The gradient rows of a chunk are
+//    assembled in class order in the staging slot their log-probs came in and leave as 16-byte streaming stores
+//    when the pair's rows are contiguous and 16-byte aligned in the gradient array.
 //  * Dynamic range.  One exponent per lane and chunk is a finite window, and peaky posteriors move 20-35 bits per
 //    frame.  A renormalised lane keeps its maximum at 2^SHIFT; a lane far below its left neighbour is pulled up to
 //    2^-GAP of it and may lose its own content, which the backward sweep does not share: its total likelihood
@@ -59,19 +61,11 @@ namespace {
 
 using namespace lattice;
 
-#ifdef MDD_PAIR_TIMING
-__device__ unsigned long long g_phase_cycles[16];
-#define PT_DECL long long pt_last = clock64(); long long pt_acc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-#define PT(i) { asm volatile("" ::: "memory"); const long long pt_now = clock64(); pt_acc[i] += pt_now - pt_last; pt_last = pt_now; }
-#define PT_FLUSH if (lane == 0) { for (int i = 0; i < 12; ++i) atomicAdd(&g_phase_cycles[i], (unsigned long long)pt_acc[i]); }
-#else
-#define PT_DECL
-#define PT(i)
-#define PT_FLUSH
-#endif
+constexpr int RAWW = 132;                  // floats per staged pair row: 2*C log-probs (C <= 63) + 2 row-LSE + pad (16 B multiple)
+constexpr int NSLOT = 3;                   // staging slots: the chunk being consumed and two in flight
 
 struct PairSmem {
-    int occ_off, rows_off, abuf_off, ckst_off, total_floats;
+    int occ_off, rows_off, abuf_off, ckst_off, raw_off, total_floats;
 };
 __host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf) {
     PairSmem s;
@@ -80,6 +74,8 @@ __host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf) {
     s.rows_off = o; o += KF * RW;                 // exp(lp) rows of the current chunk, both utterances
     s.abuf_off = o; if (!regbuf) o += KF * 32 * NSL;   // alpha label states of the chunk when they do not fit in registers
     s.ckst_off = o; o += 32 * (2 * NSL + 2);      // the next checkpoint, landing by cp.async (backward sweep)
+    o = (o + 3) & ~3;
+    s.raw_off = o; o += NSLOT * KF * RAWW;        // log-prob rows as they arrive (class order); later the gradient rows
     s.total_floats = (o + 3) & ~3;
     return s;
 }
@@ -104,6 +100,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     float* rows = base + lay.rows_off;                           // [KF][RW]
     float* abuf = base + lay.abuf_off;                           // [KF][ARS] (!REGBUF)
     float* ckst = base + lay.ckst_off;                           // [CKW]
+    float* raw = base + lay.raw_off;                             // [NSLOT][KF][RAWW]
     constexpr int OCCD = -KF * RW;                               // occupancy cell of an emission slot: rows -> occ
 
     const int C = p.C, blank = p.blank, T = p.T;
@@ -116,6 +113,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     int* lab = scratch;
     int* hist = scratch + 512;
     static_assert(2 * KF * RW >= 1280 + 288 + 128, "setup scratch must fit in the occupancy + emission rows");
+    static_assert(512 + 144 <= 1280, "label histogram [2][72] behind the labels");
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const bool have = 2 * pair + h < n_utt;
@@ -211,7 +209,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     int* ipos = scratch + 1280 + 288;                            // [2][64] class at a position, -1 = none / zero slot
     for (int i = lane; i < 128; i += 32) ipos[i] = -1;
     __syncwarp();
-    for (int c = lane; c < C; c += 32) {
+    for (int c = lane; c <= C; c += 32) {                         // item C = the zero that unused label slots read
         ipos[cpos[c]] = c;
         ipos[64 + cpos[72 + c]] = c;
     }
@@ -223,8 +221,8 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
             const int c = ipos[h * 64 + k * 32 + lane];
-            ov[h][k] = c >= 0;
-            oc[h][k] = c >= 0 ? c : 0;
+            ov[h][k] = c >= 0 && c < C;
+            oc[h][k] = ov[h][k] ? c : 0;
         }
 
     // per-lane constants: emission pointers and skip masks of my label states
@@ -259,22 +257,27 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     // 0x4B000000 are subtracted by the reader).  Integer addition is associative, so the result does not depend on the
     // order in which conflicting lanes are served: bitwise reproducible.  The cell of a class sits at the same
     // position as its emission (bank-coloured), so the emission pointers address it and the owner lane reads it back
-    // without conflicts.  Resolution 1.2e-7 of Z per product.
-    unsigned nbias[4];                                           // n_c * bias of my classes: [2*h + level]
-    for (int i = lane; i < 128; i += 32) hist[i] = 0;
+    // without conflicts.  Resolution 1.2e-7 of Z per product.  Unused label slots add the bare bias to the cell of
+    // the zero item; the lane that reads that position subtracts their count like a class's, positions nobody is
+    // placed at never change, so every cell a lane reads comes out as a plain integer and needs no masking.
+    unsigned nbias[4];                                           // n * bias of the item at my positions: [2*h + level]
+    for (int i = lane; i < 144; i += 32) hist[i] = 0;            // [2][72]: classes 0..C-1, the zero item C
     __syncwarp();
 #pragma unroll
     for (int h = 0; h < 2; ++h)
 #pragma unroll
         for (int q = 0; q < NL; ++q) {
             const int i = lane * NL + q;
-            if (i < L[h]) atomicAdd(&hist[h * 64 + lab[h * 256 + i]], 1);
+            atomicAdd(&hist[h * 72 + (i < L[h] ? lab[h * 256 + i] : C)], 1);
         }
     __syncwarp();
 #pragma unroll
     for (int h = 0; h < 2; ++h)
 #pragma unroll
-        for (int k = 0; k < 2; ++k) nbias[2 * h + k] = (unsigned)hist[h * 64 + oc[h][k]] * 0x4B000000u;
+        for (int k = 0; k < 2; ++k) {
+            const int it = ipos[h * 64 + k * 32 + lane];         // class, C = the zero item, -1 = nobody
+            nbias[2 * h + k] = it >= 0 ? (unsigned)hist[h * 72 + it] * 0x4B000000u : 0u;
+        }
     const bool isb00 = ov[0][0] && oc[0][0] == blank, isb01 = ov[0][1] && oc[0][1] == blank;
     const bool isb10 = ov[1][0] && oc[1][0] == blank, isb11 = ov[1][1] && oc[1][1] == blank;
     __syncwarp();
@@ -304,10 +307,6 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     const int bsrc0 = act[0] ? bidx[0] : bidx[1], bsrc1 = act[1] ? bidx[1] : bidx[0];
     const float* lpb0 = p.lp + (size_t)bsrc0 * p.stride_b;
     const float* lpb1 = p.lp + (size_t)bsrc1 * p.stride_b;
-    const float* lp00 = lpb0 + oc[0][0];                         // my level-0 / level-1 class of each utterance
-    const float* lp01 = lpb0 + oc[0][1];
-    const float* lp10 = lpb1 + oc[1][0];
-    const float* lp11 = lpb1 + oc[1][1];
     const size_t gstride = (size_t)p.B * C;
     float* gr0 = want_grad ? p.grad + (size_t)bidx[0] * C : nullptr;
     float* gr1 = want_grad ? p.grad + (size_t)bidx[1] * C : nullptr;
@@ -315,73 +314,109 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
 #pragma unroll
     for (int h = 0; h < 2; ++h) g[h] = act[h] ? (p.grad_out ? p.grad_out[bidx[h]] : 1.f) * p.gscalar : 0.f;
 
-    float2 pre0[CH], pre1[CH];                          // the next chunk's rows, in flight
-    // LOGITS: lane r holds -lse * log2(e) of row r of the first utterance, lane KF + r of the second; the row's
-    // emissions are then 2^(x * log2(e) - lse * log2(e)) = softmax probabilities (same instruction count: FMUL -> FFMA)
-    float nlse = 0.f;
+    // Log-prob rows travel global -> shared by cp.async in 8-byte pieces (a row of C floats is 8-byte aligned when C
+    // and the strides are even): the pair's row is 2*C/2 pieces, lane l moves pieces l and l + 32.  Staged in class
+    // order: utterance h at [h*C, h*C + C) of the slot's row, the two row-LSE values (LOGITS) behind them.
+    const bool vec8 = ((C & 1) == 0) && ((p.stride_t & 1) == 0) && ((p.stride_b & 1) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(p.lp) & 7) == 0);
+    const int hC = C >> 1;
+    const bool pv0 = lane < 2 * hC, pv1 = lane + 32 < 2 * hC;
+    const int ph0 = lane >= hC ? 1 : 0, ph1 = lane + 32 >= hC ? 1 : 0;
+    const int pd0 = 2 * lane, pd1 = 2 * (lane + 32);             // destination (floats): h*C + 2*(u - h*hC) = 2*u
+    const float* ps0 = (ph0 ? lpb1 : lpb0) + 2 * (lane - ph0 * hC);
+    const float* ps1 = (ph1 ? lpb1 : lpb0) + 2 * (lane + 32 - ph1 * hC);
     const float* lsep = nullptr;
     if constexpr (LOGITS) lsep = p.lse + ((lane & KF) ? bsrc1 : bsrc0);
-    auto load_rows = [&](auto nfc, int t0) {             // pre0[r] = (level 0, level 1) of the first utterance, ...
-        constexpr int NF = decltype(nfc)::value;
-        size_t o = (size_t)t0 * p.stride_t;
+    const unsigned raw_s = (unsigned)__cvta_generic_to_shared(raw);
+    const unsigned tstride_b = (unsigned)(p.stride_t * 4);       // row pitch in bytes (< 4 GB, checked by the launcher)
+    auto issue_rows = [&](int j) {                       // rows of chunk j -> slot j % NSLOT (its own cp.async group)
+        if (j >= 0 && j < nch) {
+            int t0;
+            const bool full = chunk_geom(j, t0);
+            const int so = (j % NSLOT) * (KF * RAWW);
+            auto body = [&](auto nfc) {
+                constexpr int NF = decltype(nfc)::value;
+                if (vec8) {
+                    const unsigned d0 = raw_s + (so + pd0) * 4, d1 = raw_s + (so + pd1) * 4;
+                    const unsigned long long o = (unsigned long long)(unsigned)t0 * tstride_b;
+                    const char* q0 = reinterpret_cast<const char*>(ps0) + o;
+                    const char* q1 = reinterpret_cast<const char*>(ps1) + o;
 #pragma unroll
-        for (int r = 0; r < NF; ++r) {
-            // volatile: these stay where they are written.  A warp waits on a scoreboard for ALL loads counted on
-            // it, so row loads issued ahead of a consumer of the checkpoint would put their DRAM latency in its way.
-            asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre0[r].x) : "l"(lp00 + o));
-            asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre0[r].y) : "l"(lp01 + o));
-            asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre1[r].x) : "l"(lp10 + o));
-            asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(pre1[r].y) : "l"(lp11 + o));
-            o += p.stride_t;
+                    for (int r = 0; r < NF; ++r) {
+                        if (pv0) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d0 + r * (RAWW * 4)), "l"(q0));
+                        if (pv1) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d1 + r * (RAWW * 4)), "l"(q1));
+                        q0 += tstride_b;
+                        q1 += tstride_b;
+                    }
+                } else {                                 // odd C / odd strides: element-wise, through registers
+                    size_t o = (size_t)t0 * p.stride_t;
+                    for (int r = 0; r < NF; ++r) {
+                        for (int i = lane; i < 2 * C; i += 32) {
+                            const int h = i >= C ? 1 : 0;
+                            raw[so + r * RAWW + i] = (h ? lpb1 : lpb0)[o + i - h * C];
+                        }
+                        o += p.stride_t;
+                    }
+                }
+                if constexpr (LOGITS) {
+                    const int r = lane & (KF - 1);
+                    if (lane < 2 * KF && r < NF)
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(raw_s + (so + r * RAWW + 2 * C + (lane >> 3)) * 4),
+                                     "l"(lsep + (size_t)(t0 + r) * p.B));
+                }
+            };
+            if (full) body(IC<CH>{});
+            else body(IC<1>{});
         }
-        if constexpr (LOGITS) {
-            nlse = 0.f;
-            if (lane < 2 * KF && (lane & (KF - 1)) < NF)
-                asm volatile("ld.global.f32 %0, [%1];" : "=f"(nlse) : "l"(lsep + (size_t)(t0 + (lane & (KF - 1))) * p.B));
+        asm volatile("cp.async.commit_group;");
+    };
+    // my four (utterance, level) items inside a staged row in class order (a position without a class reads class 0)
+    const int ro00 = oc[0][0], ro01 = oc[0][1], ro10 = C + oc[1][0], ro11 = C + oc[1][1];
+    // ... and where their exponentials / gradients go.  Stores are unconditional: a position nobody is placed at takes
+    // whatever its lane computes (nobody reads it); the lane at the zero item's position writes to a free one instead;
+    // gradient values without a class land in the pad of the staging row.
+    int wp[4], wg[4];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const unsigned free0 = __ballot_sync(FULL, ipos[h * 64 + lane] < 0), free1 = __ballot_sync(FULL, ipos[h * 64 + 32 + lane] < 0);
+        const int fpos = free0 ? __ffs(free0) - 1 : 32 + __ffs(free1) - 1;       // 64 slots, C + 1 <= 64 items: one is free
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const bool zero_item = ipos[h * 64 + k * 32 + lane] == C;
+            wp[2 * h + k] = h * CPMAX + (zero_item ? fpos : k * 32 + lane);
+            wg[2 * h + k] = ov[h][k] ? h * C + oc[h][k] : 2 * C + 2;
         }
-    };
-    auto load_chunk = [&](int j) {
-        int t0;
-        if (chunk_geom(j, t0)) load_rows(IC<CH>{}, t0);
-        else load_rows(IC<1>{}, t0);
-    };
-    auto put_row = [&](int r, float2 v0, float2 v1) {
-        float* d = rows + r * RW;
-        if (ov[0][0]) d[lane] = v0.x;
-        if (ov[0][1]) d[32 + lane] = v0.y;
-        if (ov[1][0]) d[CPMAX + lane] = v1.x;
-        if (ov[1][1]) d[CPMAX + 32 + lane] = v1.y;
-    };
-    auto row_exp = [&](int r, float ns, float2& v0, float2& v1) {
-        if constexpr (LOGITS) {
-            const float n0 = __shfl_sync(FULL, ns, r), n1 = __shfl_sync(FULL, ns, KF + r);
-            v0 = make_float2(fast_exp2(fmaf(pre0[r].x, LOG2E, n0)), fast_exp2(fmaf(pre0[r].y, LOG2E, n0)));
-            v1 = make_float2(fast_exp2(fmaf(pre1[r].x, LOG2E, n1)), fast_exp2(fmaf(pre1[r].y, LOG2E, n1)));
-        } else {
-            v0 = make_float2(fast_exp(pre0[r].x), fast_exp(pre0[r].y));
-            v1 = make_float2(fast_exp(pre1[r].x), fast_exp(pre1[r].y));
-        }
-    };
-    auto commit_rows = [&](auto nfc, bool kill0, bool kill1) {   // p = exp(lp) into shared memory; an idle half emits zeros
+    }
+    auto commit_rows = [&](auto nfc, int j, bool kill0, bool kill1) {   // p = exp(lp), bank-coloured; an idle half emits zeros
         constexpr int NF = decltype(nfc)::value;
-        const float ns = nlse * -LOG2E;
-        if (kill0 || kill1) {
+        const float* slot = raw + (j % NSLOT) * (KF * RAWW);
+        auto body = [&](auto killc) {
+            constexpr bool KILL = decltype(killc)::value != 0;
 #pragma unroll
             for (int r = 0; r < NF; ++r) {
+                const float* s = slot + r * RAWW;
                 float2 v0, v1;
-                row_exp(r, ns, v0, v1);
-                if (kill0) v0 = make_float2(0.f, 0.f);
-                if (kill1) v1 = make_float2(0.f, 0.f);
-                put_row(r, v0, v1);
+                if constexpr (LOGITS) {
+                    const float n0 = s[2 * C] * -LOG2E, n1 = s[2 * C + 1] * -LOG2E;
+                    v0 = make_float2(fast_exp2(fmaf(s[ro00], LOG2E, n0)), fast_exp2(fmaf(s[ro01], LOG2E, n0)));
+                    v1 = make_float2(fast_exp2(fmaf(s[ro10], LOG2E, n1)), fast_exp2(fmaf(s[ro11], LOG2E, n1)));
+                } else {
+                    v0 = make_float2(fast_exp(s[ro00]), fast_exp(s[ro01]));
+                    v1 = make_float2(fast_exp(s[ro10]), fast_exp(s[ro11]));
+                }
+                if constexpr (KILL) {
+                    if (kill0) v0 = make_float2(0.f, 0.f);
+                    if (kill1) v1 = make_float2(0.f, 0.f);
+                }
+                float* d = rows + r * RW;
+                d[wp[0]] = v0.x;
+                d[wp[1]] = v0.y;
+                d[wp[2]] = v1.x;
+                d[wp[3]] = v1.y;
             }
-        } else {
-#pragma unroll
-            for (int r = 0; r < NF; ++r) {
-                float2 v0, v1;
-                row_exp(r, ns, v0, v1);
-                put_row(r, v0, v1);
-            }
-        }
+        };
+        if (kill0 || kill1) body(IC<1>{});
+        else body(IC<0>{});
     };
 
     // ------------------------------------------------------------------------------------------ forward sweep
@@ -396,64 +431,38 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     int koff[2] = {0, 0};
     float* ck = ckpt_ws + (size_t)slot * n_ckpt * CKW;
 
-    PT_DECL
-    PT(0)                                               // setup
-    load_chunk(0);
+    issue_rows(0);
+    issue_rows(1);
     if (want_grad) {                                    // rows t >= T_max of the gradient are zero (torch semantics)
-        for (int t = Tmax; t < T; ++t) {
-            float* z0 = gr0 + (size_t)t * gstride;
-            float* z1 = gr1 + (size_t)t * gstride;
-            if (act[0] && ov[0][0]) __stcs(z0 + oc[0][0], 0.f);
-            if (act[0] && ov[0][1]) __stcs(z0 + oc[0][1], 0.f);
-            if (act[1] && ov[1][0]) __stcs(z1 + oc[1][0], 0.f);
-            if (act[1] && ov[1][1]) __stcs(z1 + oc[1][1], 0.f);
-        }
+        for (int t = Tmax; t < T; ++t)
+            for (int i = lane; i < C; i += 32) {
+                if (act[0]) __stcs(gr0 + (size_t)t * gstride + i, 0.f);
+                if (act[1]) __stcs(gr1 + (size_t)t * gstride + i, 0.f);
+            }
     }
 
     auto fwd_chunk = [&](auto nfc, int j, int t0) {
         constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
-#ifdef MDD_PAIR_TIMING
-        PT(2)
-        { float d2, d3;
-          asm volatile("mov.f32 %0, %2; mov.f32 %1, %3;" : "=f"(d2), "=f"(d3) : "f"(pre0[0].x), "f"(pre1[NF - 1].y));
-          if (d2 == 1.2345f && d3 == d2) flag[0] |= 1 << 30; }
-        PT(11)                                          // fwd: waiting for the rows
-#endif
+        asm volatile("cp.async.wait_group 1;" ::: "memory");     // rows of chunk j have landed (j + 1 may be in flight)
         __syncwarp();
-        commit_rows(nfc, kill0, kill1);
+        commit_rows(nfc, j, kill0, kill1);
         __syncwarp();
-        PT(8)                                           // fwd: commit
-        if (j + 1 < nch) load_chunk(j + 1);
-        if constexpr (NF == CH) {                       // rows two chunks ahead -> L2 (the next chunk's are in flight)
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                const int idx = lane + 32 * k;          // 48 tasks: row, utterance, 128-byte part of its 4*C bytes
-                const int r = idx / 6, u = (idx % 6) / 3, part = idx % 3;
-                const int t = t0 + 2 * CH + r;
-                if (idx < 6 * CH && t < Tmax) {
-                    const float* q = (u ? lpb1 : lpb0) + (size_t)t * p.stride_t + min(part * 32, C - 1);
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
-                }
-            }
-        }
+        issue_rows(j + 2);                              // into the slot chunk j - 1 was consumed from
         {
             bool ok[2];
             renorm_alpha<NSL>(a, ea, sca, lane, ok, p.strict_squash != 0, p.decay_max);
             if (!ok[0] && !kill0 && !flag[0]) flag[0] = 2 | (t0 << 8);
             if (!ok[1] && !kill1 && !flag[1]) flag[1] = 2 | (t0 << 8);
         }
-        PT(1)                                           // fwd: commit, prefetch, renormalisation
         if (want_grad) {                                // alpha entering chunk j, after its renormalisation
             float* c = ck + (size_t)j * CKW;
 #pragma unroll
-            for (int q = 0; q < NSL / 2; ++q)
-                reinterpret_cast<float4*>(c)[q * 32 + lane] = make_float4(a[2 * q].x, a[2 * q].y, a[2 * q + 1].x, a[2 * q + 1].y);
+            for (int q = 0; q < NSL; ++q) reinterpret_cast<float2*>(c)[q * 32 + lane] = a[q];   // register pairs as they are
             reinterpret_cast<int2*>(c + 64 * NSL)[lane] = make_int2(ea[0], ea[1]);
         }
 #pragma unroll
         for (int r = 0; r < NF; ++r) alpha_step<NSL>(a, sca, r * RW, bl0, bl1, ep0, ep1, ma);
-        PT(2)                                           // fwd: checkpoint store + alpha steps
         const int tend = t0 + NF;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -492,6 +501,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         if (chunk_geom(j, t0)) fwd_chunk(IC<CH>{}, j, t0);
         else fwd_chunk(IC<1>{}, j, t0);
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
     if (!want_grad || ((flag[0] || !act[0]) && (flag[1] || !act[1]))) {
 #pragma unroll
         for (int h = 0; h < 2; ++h)
@@ -507,28 +517,30 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     constexpr float FIX = 8388608.f * 0.999f;           // fixed-point scale of an occupancy fraction
     const float2 zs2 = make_float2(zi[0] * FIX, zi[1] * FIX);
     const float2 magic2 = make_float2(8388608.f, 8388608.f);
-    int bad_occ = 0;
+    unsigned occ_hi = 0u;                               // largest (row total + 8192) seen: range check of the occupancies
+
+    // The gradient rows of a chunk leave as 16-byte streaming stores of the staged row when the pair's two rows are
+    // adjacent and 16-byte aligned in the gradient array; otherwise element-wise from the same staging.
+    const bool gvec = !LIST && act[0] && act[1] && bidx[1] == bidx[0] + 1 && (C & 1) == 0 && ((p.B * C) & 3) == 0 &&
+                      (bidx[0] & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.grad) & 15) == 0);
+    const unsigned gstride_b = (unsigned)(gstride * 4);           // gradient row pitch in bytes (< 4 GB, checked by the launcher)
 
     // alpha entering chunk j (post-renormalisation) + exponents travel global -> shared by cp.async, one chunk ahead,
-    // and are picked up with LDS.  Register loads would sit on a scoreboard that the lattice's LDS consumers share
-    // (a warp waits for ALL loads counted on a scoreboard), so every such consumer would wait for their L2 latency.
+    // and are picked up with LDS.
     const unsigned ckst_s = (unsigned)__cvta_generic_to_shared(ckst);
     auto ckpt_issue = [&](int j) {
-        const float* c = ck + (size_t)j * CKW;
+        if (j >= 0) {
+            const float* c = ck + (size_t)j * CKW;
 #pragma unroll
-        for (int q = 0; q < NSL / 2; ++q)
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ckst_s + (q * 32 + lane) * 16), "l"(c + (q * 32 + lane) * 4));
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ckst_s + (64 * NSL + lane * 2) * 4), "l"(c + 64 * NSL + lane * 2));
+            for (int q = 0; q < NSL / 2; ++q)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ckst_s + (q * 32 + lane) * 16), "l"(c + (q * 32 + lane) * 4));
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ckst_s + (64 * NSL + lane * 2) * 4), "l"(c + 64 * NSL + lane * 2));
+        }
         asm volatile("cp.async.commit_group;");
     };
     auto ckpt_take = [&]() {
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
 #pragma unroll
-        for (int q = 0; q < NSL / 2; ++q) {
-            const float4 v = reinterpret_cast<const float4*>(ckst)[q * 32 + lane];
-            a[2 * q] = make_float2(v.x, v.y);
-            a[2 * q + 1] = make_float2(v.z, v.w);
-        }
+        for (int q = 0; q < NSL; ++q) a[q] = reinterpret_cast<const float2*>(ckst)[q * 32 + lane];
         const int2 e = reinterpret_cast<const int2*>(ckst + 64 * NSL)[lane];
         ea[0] = e.x; ea[1] = e.y;
     };
@@ -536,20 +548,13 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     auto bwd_chunk = [&](auto nfc, int j, int t0) {
         constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
+        // in flight, oldest first: rows(j), checkpoint(j), rows(j-1): everything but the newest has landed
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncwarp();
         ckpt_take();
-        if (j < nch - 1) {                              // the last chunk is still staged (and exponentiated)
-            __syncwarp();
-            commit_rows(nfc, kill0, kill1);
-            __syncwarp();
-        }
-        PT(9)                                           // bwd: commit + row loads
-#ifdef MDD_PAIR_TIMING
-        { int d0, d1; float d2, d3;                       // real consumers: wait for the checkpoint to land
-          asm volatile("mov.b32 %0, %4; mov.b32 %1, %5; mov.f32 %2, %6; mov.f32 %3, %7;"
-                       : "=r"(d0), "=r"(d1), "=f"(d2), "=f"(d3) : "r"(ea[0]), "r"(ea[1]), "f"(a[0].x), "f"(a[NSL - 1].y));
-          if (d0 == 0x7fffffff && d1 == d0 && d2 == 1.2345f && d3 == d2) flag[0] |= 1 << 30; }
-        PT(10)                                          // bwd: waiting for the checkpoint
-#endif
+        if (j < nch - 1) commit_rows(nfc, j, kill0, kill1);       // the last chunk is still staged (and exponentiated)
+        __syncwarp();
+        ckpt_issue(j - 1);                              // the staging block has been read
         // a / ea hold the checkpoint of this chunk: boundary factors and the beta exponents that go with it
         float2 scb, scb2;
         {
@@ -579,15 +584,16 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
             scb2 = make_float2(sb2[0], sb2[1]);
             const float2 f2 = make_float2(fb[0], fb[1]), f22 = make_float2(fb2[0], fb2[1]);
 #pragma unroll
-            for (int jj = 0; jj < NSL; ++jj) {
-                bt[jj] = __fmul2_rn(__fmul2_rn(bt[jj], f2), f22);
-                const int s = lane * NSL + jj;
-                if (s == S[0] - 1) bt[jj].x += ini[0];
-                if (s == S[1] - 1) bt[jj].y += ini[1];
+            for (int jj = 0; jj < NSL; ++jj) bt[jj] = __fmul2_rn(__fmul2_rn(bt[jj], f2), f22);
+            if ((act[0] && tend == Tb[0]) || (act[1] && tend == Tb[1])) {   // once per utterance: beta_T enters
+#pragma unroll
+                for (int jj = 0; jj < NSL; ++jj) {
+                    const int s = lane * NSL + jj;
+                    if (s == S[0] - 1) bt[jj].x += ini[0];
+                    if (s == S[1] - 1) bt[jj].y += ini[1];
+                }
             }
         }
-        if (j < nch - 1 && j > 0) load_chunk(j - 1);    // after the checkpoint's consumers (see load_rows)
-        PT(3)                                           // bwd: commit, exponent bookkeeping, row loads
         // recompute alpha over the chunk, keeping the label states
         float2 A[REGBUF ? NF : 1][NL];
 #pragma unroll
@@ -599,10 +605,9 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
                 else reinterpret_cast<float2*>(abuf + r * ARS)[q * 32 + lane] = a[2 * q + 1];
             }
         }
-        if (j > 0) ckpt_issue(j - 1);                   // the alpha registers are free: the next checkpoint sets off
+        issue_rows(j - 2);                              // into the slot the gradient rows of chunk j + 1 have left
         __syncwarp();                                   // the previous chunk's gradient rows have been read
-        PT(4)                                           // bwd: alpha recomputation
-        // beta over the chunk; label products alpha_t(s) * u_t(s) into their class-sorted slots
+        // beta over the chunk; label products alpha_t(s) * u_t(s) into the class cells
 #pragma unroll
         for (int r = NF - 1; r >= 0; --r) {
             float2 ul[NL], al[NL];
@@ -619,70 +624,81 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
                 atomicAdd(reinterpret_cast<unsigned*>(const_cast<float*>(ep1[q])) + (OCCD + r * RW), __float_as_uint(fx.y));
             }
         }
-        if (j >= 2) {                                   // rows two chunks down -> L2 (the next chunk's are in flight)
-            int tq;
-            if (chunk_geom(j - 2, tq)) {
+        __syncwarp();
+        // gradient rows of the chunk: (softmax prob - occupancy / Z) * g, assembled in class order in the staging slot
+        // the chunk's log-probs arrived in; the cells are zeroed for the next chunk
+        {
+            const float g0 = kill0 ? 0.f : g[0], g1 = kill1 ? 0.f : g[1];
+            const float og0 = g0 * (1.f / FIX), og1 = g1 * (1.f / FIX);
+            float* gs = raw + (j % NSLOT) * (KF * RAWW);
+            constexpr int fixi = (int)FIX;
+            // one row ahead: cells and their warp totals (REDUX) of row r + 1 are on their way while row r is finished
+            int oc4[4], on4[4] = {0, 0, 0, 0}, ts0, ts1, tn0 = 0, tn1 = 0;
+            auto cells = [&](int r, int (&o)[4], int& s0, int& s1) {
+                unsigned* oq = occ + r * RW;
+                o[0] = (int)(oq[lane] - nbias[0]);
+                o[1] = (int)(oq[32 + lane] - nbias[1]);
+                o[2] = (int)(oq[CPMAX + lane] - nbias[2]);
+                o[3] = (int)(oq[CPMAX + 32 + lane] - nbias[3]);
+                oq[lane] = 0u; oq[32 + lane] = 0u; oq[CPMAX + lane] = 0u; oq[CPMAX + 32 + lane] = 0u;
+                s0 = __reduce_add_sync(FULL, o[0] + o[1]);       // blank: what the label classes leave of Z
+                s1 = __reduce_add_sync(FULL, o[2] + o[3]);
+            };
+            cells(0, oc4, ts0, ts1);
 #pragma unroll
-                for (int k = 0; k < 2; ++k) {
-                    const int idx = lane + 32 * k;      // 48 tasks: row, utterance, 128-byte part of its 4*C bytes
-                    const int r = idx / 6, u = (idx % 6) / 3, part = idx % 3;
-                    if (idx < 6 * CH) {
-                        const float* q = (u ? lpb1 : lpb0) + (size_t)(tq + r) * p.stride_t + min(part * 32, C - 1);
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+            for (int r = 0; r < NF; ++r) {
+                if (r + 1 < NF) cells(r + 1, on4, tn0, tn1);
+                const float* d = rows + r * RW;
+                const float2 pv0 = make_float2(d[lane], d[32 + lane]), pv1 = make_float2(d[CPMAX + lane], d[CPMAX + 32 + lane]);
+                if (isb00) oc4[0] = fixi - ts0;
+                if (isb01) oc4[1] = fixi - ts0;
+                if (isb10) oc4[2] = fixi - ts1;
+                if (isb11) oc4[3] = fixi - ts1;
+                // every row total must be a fraction of Z in [0, 1] up to rounding: catches overflow / NaN upstream
+                occ_hi = max(occ_hi, max((unsigned)(ts0 + 8192), (unsigned)(ts1 + 8192)));
+                float* w = gs + r * RAWW;
+                w[wg[0]] = fmaf(-(float)oc4[0], og0, pv0.x * g0);
+                w[wg[1]] = fmaf(-(float)oc4[1], og0, pv0.y * g0);
+                w[wg[2]] = fmaf(-(float)oc4[2], og1, pv1.x * g1);
+                w[wg[3]] = fmaf(-(float)oc4[3], og1, pv1.y * g1);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) oc4[k] = on4[k];
+                ts0 = tn0; ts1 = tn1;
+            }
+            __syncwarp();
+            if (gvec) {                                 // the pair's two rows are one 16-byte aligned run of 2*C floats
+                char* gq = reinterpret_cast<char*>(gr0) + (unsigned long long)(unsigned)t0 * gstride_b + lane * 16;
+#pragma unroll
+                for (int r = 0; r < NF; ++r) {
+                    if (lane < C / 2) __stcs(reinterpret_cast<float4*>(gq), reinterpret_cast<const float4*>(gs + r * RAWW)[lane]);
+                    gq += gstride_b;
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < NF; ++r) {
+                    const size_t go = (size_t)(t0 + r) * gstride;
+                    for (int i = lane; i < C; i += 32) {
+                        if (act[0]) __stcs(gr0 + go + i, gs[r * RAWW + i]);
+                        if (act[1]) __stcs(gr1 + go + i, gs[r * RAWW + C + i]);
                     }
                 }
             }
         }
-        __syncwarp();
-        PT(5)                                           // bwd: beta + occupancy accumulation
-        // gradient rows of the chunk: (softmax prob - occupancy / Z) * g; the cells are zeroed for the next chunk
-        {
-            const float g0 = kill0 ? 0.f : g[0], g1 = kill1 ? 0.f : g[1];
-            const float og0 = g0 * (1.f / FIX), og1 = g1 * (1.f / FIX);
-            const bool s00 = act[0] && ov[0][0], s01 = act[0] && ov[0][1], s10 = act[1] && ov[1][0], s11 = act[1] && ov[1][1];
-            float* w00 = gr0 + (size_t)t0 * gstride + oc[0][0];
-            float* w01 = gr0 + (size_t)t0 * gstride + oc[0][1];
-            float* w10 = gr1 + (size_t)t0 * gstride + oc[1][0];
-            float* w11 = gr1 + (size_t)t0 * gstride + oc[1][1];
-            constexpr int OMAX = (int)(8388608.0 * 1.002);      // a fraction of Z above 1 (+ rounding): upstream overflow
-#pragma unroll
-            for (int r = 0; r < NF; ++r) {
-                const float* d = rows + r * RW;
-                unsigned* oq = occ + r * RW;
-                const float2 pv0 = make_float2(d[lane], d[32 + lane]), pv1 = make_float2(d[CPMAX + lane], d[CPMAX + 32 + lane]);
-                int o00 = (int)(oq[lane] - nbias[0]), o01 = (int)(oq[32 + lane] - nbias[1]);
-                int o10 = (int)(oq[CPMAX + lane] - nbias[2]), o11 = (int)(oq[CPMAX + 32 + lane] - nbias[3]);
-                oq[lane] = 0u; oq[32 + lane] = 0u; oq[CPMAX + lane] = 0u; oq[CPMAX + 32 + lane] = 0u;
-                // blank: what the label classes leave of Z
-                const int t0s = __reduce_add_sync(FULL, (ov[0][0] ? o00 : 0) + (ov[0][1] ? o01 : 0));
-                const int t1s = __reduce_add_sync(FULL, (ov[1][0] ? o10 : 0) + (ov[1][1] ? o11 : 0));
-                const int fixi = (int)FIX;
-                if (isb00) o00 = fixi - t0s;
-                if (isb01) o01 = fixi - t0s;
-                if (isb10) o10 = fixi - t1s;
-                if (isb11) o11 = fixi - t1s;
-                // every occupancy must be a fraction of Z in [0, 1] up to rounding: catches overflow / NaN upstream
-                if (!kill0 && ((unsigned)(t0s + 8192) > (unsigned)(OMAX + 8192))) bad_occ |= 1;
-                if (!kill1 && ((unsigned)(t1s + 8192) > (unsigned)(OMAX + 8192))) bad_occ |= 2;
-                if (s00) __stcs(w00, fmaf(-(float)o00, og0, pv0.x * g0));
-                if (s01) __stcs(w01, fmaf(-(float)o01, og0, pv0.y * g0));
-                if (s10) __stcs(w10, fmaf(-(float)o10, og1, pv1.x * g1));
-                if (s11) __stcs(w11, fmaf(-(float)o11, og1, pv1.y * g1));
-                w00 += gstride; w01 += gstride; w10 += gstride; w11 += gstride;
-            }
-        }
-        PT(7)                                           // bwd: gradient rows
     };
 
-    if (nch >= 2) load_chunk(nch - 2);
+    // in flight when chunk j starts, oldest first: rows(j), checkpoint(j), rows(j - 1); the last chunk's rows are
+    // still staged from the forward sweep
     ckpt_issue(nch - 1);
+    issue_rows(nch - 2);
     for (int j = nch - 1; j >= 0; --j) {
         int t0;
         if (chunk_geom(j, t0)) bwd_chunk(IC<CH>{}, j, t0);
         else bwd_chunk(IC<1>{}, j, t0);
     }
-    PT_FLUSH
+    asm volatile("cp.async.wait_all;" ::: "memory");
     {   // beta must have stayed finite to the very first frame (a blank state's overflow shows nowhere else)
+        constexpr unsigned OMAX = (unsigned)(8388608.0 * 1.002) + 8192u;   // a row total above Z (+ rounding): upstream overflow
+        int bad_occ = occ_hi > OMAX ? 3 : 0;            // which of the two is decided below by the likelihood check
 #pragma unroll
         for (int jj = 0; jj < NSL; ++jj) {
             if (!(bt[jj].x < 3.0e38f)) bad_occ |= 1;
@@ -707,7 +723,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         }
 #pragma unroll
         for (int h = 0; h < 2; ++h)
-            if (act[h] && lane == 0) p.flags[bidx[h]] = flag[h];   // 0 = done here; else redone in log space
+            if (act[h] && lane == 0) p.flags[bidx[h]] = flag[h];   // 0 = done here; else redone by the next tier
     }
 }
 
@@ -850,17 +866,6 @@ int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
 }  // namespace
 
 #if !MDD_PAIR_TU_LOGITS
-#ifdef MDD_PAIR_TIMING
-extern "C" void mdd_debug_phase_cycles(unsigned long long* out, int reset) {
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(out, g_phase_cycles, sizeof(unsigned long long) * 16);
-    if (reset) {
-        unsigned long long z[16] = {0};
-        cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z));
-    }
-}
-#endif
-
 bool ctc_pair_supported(int C, int Lmax) { return C <= 63 && pick_nsl(Lmax) != 0; }   // C classes + the zero item <= 64 slots
 
 size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
