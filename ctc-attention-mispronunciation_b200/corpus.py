@@ -131,6 +131,12 @@ class CorpusMDD:
         self.totals += r["totals"].cpu().numpy()
         return r
 
+    def scoring(self, m_speaker=False):
+        """FAR / FRR / DER and the other rates of the offline scorer from this evaluator's totals (see scoring_rates):
+        its per-error-type counters collapse onto TA / FR / FA / correct / wrong diagnosis."""
+        ta, fr, fa, trc, trw = (int(x) for x in self.totals[1 if m_speaker else 0][:5])
+        return scoring_rates({"cor_cor": ta, "cor_nocor": fr, "sub_nosub": fa, "sub_sub": trc, "sub_sub1": trw})
+
     def summary(self):
         """Reference-named counters and the rates printed at test_ctc_nosil.py:299-343 (ZeroDivisionError included)."""
         out = {}
@@ -146,3 +152,42 @@ class CorpusMDD:
                 out.update({tag + "PER": float(errs) / nlab * 100, tag + "precision": p * 100, tag + "recall": r * 100,
                             tag + "f1": 2 * p * r / (p + r) * 100})
         return out
+
+
+SCORING_COUNTERS = ("cor_cor", "cor_nocor", "sub_sub", "sub_sub1", "sub_nosub", "ins_ins", "ins_ins1", "ins_noins",
+                    "del_del", "del_del1", "del_nodel")
+
+
+def scoring_rates(counters):
+    """The rates egs/attention_aug/result/utils/scoring/ins_del_sub_cor_analysis.py:193-219 derives from its eleven
+    counters (x_x: error of type x detected and diagnosed correctly, x_x1: detected with the wrong diagnosis, x_nox:
+    accepted; cor_cor / cor_nocor: correct phones accepted / rejected).  Missing counters count as 0.
+    ZeroDivisionError where the reference raises it."""
+    c = {k: int(counters.get(k, 0)) for k in SCORING_COUNTERS}
+    total = sum(c.values())
+    tp = c["sub_sub"] + c["ins_ins"] + c["del_del"] + c["sub_sub1"] + c["ins_ins1"] + c["del_del1"]
+    fp = c["cor_nocor"]
+    fn = c["sub_nosub"] + c["ins_noins"] + c["del_nodel"]
+    recall = tp / (tp + fn)
+    precision = tp / (tp + fp)
+    correct_diag = c["sub_sub"] + c["ins_ins"] + c["del_del"]
+    error_diag = c["sub_sub1"] + c["ins_ins1"] + c["del_del1"]
+    err_count = tp + fn
+    return {"sum": total, "recall": recall, "precision": precision, "f1": 2 * precision * recall / (recall + precision),
+            "TA": c["cor_cor"] / (c["cor_cor"] + c["cor_nocor"]), "n_TA": c["cor_cor"],
+            "FR": c["cor_nocor"] / (c["cor_cor"] + c["cor_nocor"]), "n_FR": c["cor_nocor"],
+            "FA": fn / err_count, "n_FA": fn,
+            "correct_diag": correct_diag / (correct_diag + error_diag), "n_correct_diag": correct_diag,
+            "error_diag": error_diag / (correct_diag + error_diag), "n_error_diag": error_diag,
+            "FAR": 1 - recall, "FRR": c["cor_nocor"] / (c["cor_nocor"] + c["cor_cor"]),
+            "DER": error_diag / (error_diag + correct_diag)}
+
+
+def scoring_report(counters):
+    """The text ins_del_sub_cor_analysis.py:194-219 prints, byte for byte."""
+    r = scoring_rates(counters)
+    return ("sum: %d\n" % r["sum"] + "Recall: %.4f\n" % r["recall"] + "Precision: %.4f\n" % r["precision"]
+            + "f1:%.4f\n" % r["f1"] + "TA: %.4f %d\n" % (r["TA"], r["n_TA"]) + "FR: %.4f %d\n" % (r["FR"], r["n_FR"])
+            + "FA: %.4f %d\n" % (r["FA"], r["n_FA"]) + "Correct Diag: %.4f %d\n" % (r["correct_diag"], r["n_correct_diag"])
+            + "Error Diag: %.4f %d\n" % (r["error_diag"], r["n_error_diag"]) + "FAR: %.4f\n" % r["FAR"]
+            + "FRR: %.4f\n" % r["FRR"] + "DER: %.4f\n" % r["DER"])

@@ -826,7 +826,12 @@ constexpr int CH2 = 2;                                           // chunk length
 template <int NSL, bool REGBUF, int MAXR, bool LOGITS>
 int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
     const int npairs = (p.B + 1) / 2;
-    int rc = launch_cfg1<NSL, REGBUF, MAXR, LOGITS, KF, false>(p, ws, st, npairs);
+    // Few pairs per SM: one CTA per pair with helper warps (ctc_team.cu) -- nothing hides a lone warp's latencies here.
+    static int team_max = env_int("MDD_CTC_TEAM_MAX_PAIRS", 2 * kNumSM);
+    const bool team_ok = ctc_team_supported(p.C, p.Lmax);
+    int rc;
+    if (team_ok && npairs <= team_max) rc = launch_ctc_team(p, ws, st, false, npairs);
+    else rc = launch_cfg1<NSL, REGBUF, MAXR, LOGITS, KF, false>(p, ws, st, npairs);
     if (rc || !p.list) return rc;
     // second tier: the flagged utterances again, renormalised every CH2 frames, in the same checkpoint workspace
     const size_t ws_floats = (size_t)npairs * (p.T / KF + 2 * KF) * PGeo<NSL>::CKW;
@@ -836,6 +841,8 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
     compact_flagged_kernel<<<1, 1024, 0, st>>>(p.flags, p.B, p.list, p.list_count);
     MDD_CHECK_LAUNCH();
     p.list_cap_pairs = cap;
+    static int team_tier2 = env_int("MDD_CTC_TEAM_TIER2", 1);
+    if (team_ok && team_tier2) return launch_ctc_team(p, ws, st, true, std::min(cap, 2 * sm_count()));
     return launch_cfg1<NSL, REGBUF, MAXR, LOGITS, CH2, true>(p, ws, st, cap);
 }
 

@@ -50,6 +50,10 @@ bool ctc_pair_supported(int C, int Lmax);
 size_t ctc_pair_ws_bytes(int T, int B, int Lmax);
 int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st);
 
+// one CTA per pair, lattice warp + helper warps (ctc_team.cu): few utterances per SM, and the second tier
+bool ctc_team_supported(int C, int Lmax);
+int launch_ctc_team(const CtcParams& p, void* ws, cudaStream_t st, bool list, int nblocks);
+
 // per-frame log-sum-exp (+ argmax) of logits (row_lse.cu): the pre-pass of mdd_ctc_loss_logits
 int launch_row_lse(const float* x, int T, int B, int C, int64_t stride_t, int64_t stride_b, float* lse, uint8_t* amax,
                    cudaStream_t st);

@@ -531,6 +531,29 @@ def gen_textio(vocab):
     jdump("textio.json.gz", {"batches": batches, "logs": logs, "ipa": ipa})
 
 
+def gen_scoring():
+    """The offline half of the corpus evaluation: the rates (recall / precision / f1, TA / FR / FA, Correct / Error
+    Diag, FAR / FRR / DER) that result/utils/scoring/ins_del_sub_cor_analysis.py:193-219 prints from its eleven
+    counters.  The counting loop above those lines reads Kaldi align-text output, which this image cannot produce;
+    lines 193-219 are executed verbatim on injected counters and their printed text is recorded."""
+    import contextlib
+    import io
+    path = os.path.join(RL.eg_dir(), "result", "utils", "scoring", "ins_del_sub_cor_analysis.py")
+    src = "".join(open(path).readlines()[192:219])
+    assert src.startswith("sum1 = cor_cor"), src[:40]
+    names = ["cor_cor", "cor_nocor", "sub_sub", "sub_sub1", "sub_nosub", "ins_ins", "ins_ins1", "ins_noins", "del_del",
+             "del_del1", "del_nodel"]
+    rng = np.random.default_rng(17)
+    cases = []
+    for k in range(12):
+        c = {n: int(rng.integers(1, 4000 if k % 3 else 40)) for n in names}
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            exec(compile(src, path, "exec"), dict(c))
+        cases.append({"counters": c, "text": buf.getvalue()})
+    jdump("scoring_rates.json.gz", {"names": names, "cases": cases})
+
+
 def main():
     assert RL.available(), "reference tree not mounted"
     os.makedirs(os.path.join(GOLD, "assets"), exist_ok=True)
@@ -538,13 +561,13 @@ def main():
     shutil.copy(RL.arpa_path(), os.path.join(GOLD, "assets", "lm_phone_bg.arpa"))
     vocab43 = RL.units_vocab()
     assert len(vocab43) == 43, len(vocab43)
-    steps = sys.argv[1:] or ["ctc", "ctc_logits", "greedy", "beam_small", "beam_c4", "lm", "wer", "mdd", "c1", "corpus", "textio"]
+    steps = sys.argv[1:] or ["ctc", "ctc_logits", "greedy", "beam_small", "beam_c4", "lm", "wer", "mdd", "c1", "corpus", "textio", "scoring"]
     for s in steps:
         print("==", s, flush=True)
         {"ctc": gen_ctc, "ctc_logits": gen_ctc_logits, "greedy": lambda: gen_greedy(vocab43), "beam_small": lambda: gen_beam_small(vocab43),
          "beam_c4": lambda: gen_beam_c4(vocab43), "lm": lambda: gen_lm_table(vocab43), "wer": gen_wer_corpus,
          "mdd": lambda: gen_mdd_post(vocab43), "c1": lambda: gen_c1(vocab43),
-         "corpus": lambda: gen_corpus(vocab43), "textio": lambda: gen_textio(vocab43)}[s]()
+         "corpus": lambda: gen_corpus(vocab43), "textio": lambda: gen_textio(vocab43), "scoring": gen_scoring}[s]()
 
 
 if __name__ == "__main__":

@@ -212,3 +212,16 @@ def test_bucketed_batches_cover_and_bound_waste():
     assert all(max(lens[i] for i in b) - min(lens[i] for i in b) < 64 for b in batches)
     again = textio.bucketed_batches(lens, batch_size=32, width=64, shuffle_seed=3)
     assert sorted(map(tuple, again)) == sorted(map(tuple, batches)) and again != batches
+
+
+def test_scoring_rates_match_reference_script(M):
+    """FAR / FRR / DER (and the rest) against the text ins_del_sub_cor_analysis.py:193-219 printed on the same counters."""
+    from conftest import jload
+    from mddctc.corpus import CorpusMDD, scoring_rates, scoring_report
+    for case in jload("scoring_rates.json.gz")["cases"]:
+        assert scoring_report(case["counters"]) == case["text"]
+    ev = CorpusMDD({0: "blank", 1: "a", 2: "b"})
+    ev.totals[0][:5] = [90, 10, 5, 30, 15]                  # TA, FR, FA, correct diagnosis, wrong diagnosis
+    r = ev.scoring()
+    assert abs(r["FRR"] - 0.1) < 1e-12 and abs(r["FAR"] - 5 / 50) < 1e-12 and abs(r["DER"] - 15 / 45) < 1e-12
+    assert r == scoring_rates({"cor_cor": 90, "cor_nocor": 10, "sub_nosub": 5, "sub_sub": 30, "sub_sub1": 15})
