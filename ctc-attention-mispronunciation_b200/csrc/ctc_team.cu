@@ -31,13 +31,24 @@ constexpr int TRAWW = 132;                 // floats per staged pair row: 2*C lo
 constexpr int TNSLOT = 3;                  // raw staging slots (chunk % 3)
 constexpr int TNE = 3;                     // emission buffers (chunk % 3)
 
+#ifdef MDD_TEAM_TIMING
+__device__ unsigned long long g_team_cycles[32];
+#define TT_DECL long long tt_last = clock64(); long long tt_acc[16] = {0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0};
+#define TT(i) { asm volatile("" ::: "memory"); const long long tt_now = clock64(); tt_acc[i] += tt_now - tt_last; tt_last = tt_now; }
+#define TT_FLUSH(base) if (lane == 0 && blockIdx.x == 0) { for (int i = 0; i < 16; ++i) atomicAdd(&g_team_cycles[(base) + i], (unsigned long long)tt_acc[i]); }
+#else
+#define TT_DECL
+#define TT(i)
+#define TT_FLUSH(base)
+#endif
+
 __device__ __forceinline__ void mbar_inval(uint64_t* bar) {
     asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 template <int NSL, int NH>
 struct TeamLayout {
-    static constexpr int RPH = (KF + NH - 1) / NH;              // rows per helper and chunk
+    static constexpr int RPH = (KF + NH - 1) / NH;              // rows per helper and chunk (at most)
     static constexpr int CKW = PGeo<NSL>::CKW;
     static constexpr int E_OFF = 0;                             // [TNE][KF][RW] emissions
     static constexpr int OCC_OFF = E_OFF + TNE * KF * RW;       // [2][KF][RW] class cells
@@ -261,23 +272,30 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
         const float* ps1 = (ph1 ? lpb1 : lpb0) + 2 * (lane + 32 - ph1 * hC);
         const unsigned raw_s = smem_u32(raw);
 
+        // A full chunk gives every helper CH / NH rows (r = hid, hid + NH, ...), handled as straight-line code so that
+        // the rows' latencies overlap; the single frames at the end of a phase belong to helper 0.
+        static_assert(CH % NH == 0, "a full chunk must split evenly over the helpers");
+        const unsigned tstride_b = (unsigned)(p.stride_t * 4);   // row pitch in bytes (< 4 GB, checked by the launcher)
         auto issue_rows = [&](int j) {                   // my rows of chunk j -> slot j % TNSLOT (one cp.async group)
             if (j >= 0 && j < nch) {
                 int t0;
-                const int nf = chunk_geom(j, t0) ? CH : 1;
+                const bool full = chunk_geom(j, t0);
                 const int so = (j % TNSLOT) * (KF * TRAWW);
+                auto body = [&](auto nrc, int r0, int rs) {
+                    constexpr int NR = decltype(nrc)::value;
 #pragma unroll
-                for (int k = 0; k < RPH; ++k) {
-                    const int r = hid + k * NH;
-                    if (r < nf) {
-                        const size_t o = (size_t)(t0 + r) * p.stride_t;
+                    for (int k = 0; k < NR; ++k) {
+                        const int r = r0 + k * rs;
+                        const unsigned long long o = (unsigned long long)(unsigned)(t0 + r) * tstride_b;
                         if (vec8) {
-                            if (pv0) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(raw_s + (so + r * TRAWW + pd0) * 4), "l"(ps0 + o));
-                            if (pv1) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(raw_s + (so + r * TRAWW + pd1) * 4), "l"(ps1 + o));
+                            if (pv0) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(raw_s + (so + r * TRAWW + pd0) * 4),
+                                                  "l"(reinterpret_cast<const char*>(ps0) + o));
+                            if (pv1) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(raw_s + (so + r * TRAWW + pd1) * 4),
+                                                  "l"(reinterpret_cast<const char*>(ps1) + o));
                         } else {
                             for (int i = lane; i < 2 * C; i += 32) {
                                 const int h = i >= C ? 1 : 0;
-                                raw[so + r * TRAWW + i] = (h ? lpb1 : lpb0)[o + i - h * C];
+                                raw[so + r * TRAWW + i] = (h ? lpb1 : lpb0)[(size_t)(t0 + r) * p.stride_t + i - h * C];
                             }
                         }
                         if constexpr (LOGITS) {
@@ -286,20 +304,23 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
                                              "l"(p.lse + (size_t)(t0 + r) * p.B + (lane ? bsrc1 : bsrc0)));
                         }
                     }
-                }
+                };
+                if (full) body(IC<CH / NH>{}, hid, NH);
+                else if (hid == 0) body(IC<1>{}, 0, 1);
             }
             asm volatile("cp.async.commit_group;");
         };
         auto commit_rows = [&](int j) {                  // my rows of chunk j: exp(lp), bank-coloured, into E[j % TNE]
             int t0;
-            const int nf = chunk_geom(j, t0) ? CH : 1;
+            const bool full = chunk_geom(j, t0);
             const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
             const float* slotp = raw + (j % TNSLOT) * (KF * TRAWW);
             float* Eb = E + (j % TNE) * (KF * RW);
+            auto body = [&](auto nrc, int r0, int rs) {
+                constexpr int NR = decltype(nrc)::value;
 #pragma unroll
-            for (int k = 0; k < RPH; ++k) {
-                const int r = hid + k * NH;
-                if (r < nf) {
+                for (int k = 0; k < NR; ++k) {
+                    const int r = r0 + k * rs;
                     const float* s = slotp + r * TRAWW;
                     float2 v0, v1;
                     if constexpr (LOGITS) {
@@ -318,7 +339,9 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
                     d[wp[2]] = v1.x;
                     d[wp[3]] = v1.y;
                 }
-            }
+            };
+            if (full) body(IC<CH / NH>{}, hid, NH);
+            else if (hid == 0) body(IC<1>{}, 0, 1);
         };
         auto arrive = [&](uint64_t* bar) {
             __syncwarp();
@@ -337,16 +360,20 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
         unsigned ph_free = 0u;                           // parity to wait for next, per e_free barrier
         issue_rows(0);
         issue_rows(1);
+        TT_DECL
         for (int j = 0; j < nch; ++j) {
             asm volatile("cp.async.wait_group 1;" ::: "memory");
             __syncwarp();
+            TT(0)                                        // helper fwd: wait rows
             if (j >= TNE) {                              // the lattice warp has left the buffer (chunk j - TNE)
                 mbar_wait(&e_free[j % TNE], (ph_free >> (j % TNE)) & 1u);
                 ph_free ^= 1u << (j % TNE);
             }
+            TT(1)                                        // helper fwd: wait e_free
             commit_rows(j);
             arrive(&e_full[j % TNE]);
             issue_rows(j + 2);
+            TT(2)                                        // helper fwd: commit + issue
         }
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();                                 // (A) forward done; the lattice warp decides whether to go on
@@ -359,20 +386,25 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
         unsigned occ_hi = 0u;
         unsigned ph_occ = 0u;                            // parity per occ_full barrier
         float* mygst = gst + hid * (RPH * TRAWW);
+        const bool gvec = (C & 1) == 0 && ((reinterpret_cast<uintptr_t>(p.grad) & 7) == 0);   // 8-byte stores of a row
+        const unsigned gstride_b = (unsigned)(gstride * 4);
         auto gradient_rows = [&](int j, int nb) {        // my rows of chunk j (the nb-th chunk of the backward sweep)
             int t0;
-            const int nf = chunk_geom(j, t0) ? CH : 1;
+            const bool full = chunk_geom(j, t0);
             const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
             const float g0 = kill0 ? 0.f : g[0], g1 = kill1 ? 0.f : g[1];
             const float og0 = g0 * (1.f / FIX), og1 = g1 * (1.f / FIX);
+            TT(3)                                        // helper bwd: commit / issue
             mbar_wait(&occ_full[nb & 1], (ph_occ >> (nb & 1)) & 1u);
             ph_occ ^= 1u << (nb & 1);
+            TT(4)                                        // helper bwd: wait occ_full
             const float* Eb = E + (j % TNE) * (KF * RW);
             unsigned* ob = occ + (nb & 1) * (KF * RW);
+            auto cells = [&](auto nrc, int r0, int rs) {
+                constexpr int NR = decltype(nrc)::value;
 #pragma unroll
-            for (int k = 0; k < RPH; ++k) {
-                const int r = hid + k * NH;
-                if (r < nf) {
+                for (int k = 0; k < NR; ++k) {
+                    const int r = r0 + k * rs;
                     const float* d = Eb + r * RW;
                     unsigned* oq = ob + r * RW;
                     int o00 = (int)(oq[lane] - nbias[0]), o01 = (int)(oq[32 + lane] - nbias[1]);
@@ -392,35 +424,57 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
                     w[wg[2]] = fmaf(-(float)o10, og1, pv1.x * g1);
                     w[wg[3]] = fmaf(-(float)o11, og1, pv1.y * g1);
                 }
-            }
-            arrive(&occ_free[nb & 1]);                   // cells are zero again (and my staged rows are complete)
+            };
+            auto stores = [&](auto nrc, int r0, int rs) {
+                constexpr int NR = decltype(nrc)::value;
 #pragma unroll
-            for (int k = 0; k < RPH; ++k) {
-                const int r = hid + k * NH;
-                if (r < nf) {
-                    const size_t go = (size_t)(t0 + r) * gstride;
-                    for (int i = lane; i < C; i += 32) {
-                        if (act[0]) __stcs(gr0 + go + i, mygst[k * TRAWW + i]);
-                        if (act[1]) __stcs(gr1 + go + i, mygst[k * TRAWW + C + i]);
+                for (int k = 0; k < NR; ++k) {
+                    const int r = r0 + k * rs;
+                    const unsigned long long go = (unsigned long long)(unsigned)(t0 + r) * gstride_b;
+                    const float* w = mygst + k * TRAWW;
+                    if (gvec) {
+                        if (lane < C / 2) {
+                            if (act[0]) __stcs(reinterpret_cast<float2*>(reinterpret_cast<char*>(gr0) + go) + lane, reinterpret_cast<const float2*>(w)[lane]);
+                            if (act[1]) __stcs(reinterpret_cast<float2*>(reinterpret_cast<char*>(gr1) + go) + lane, reinterpret_cast<const float2*>(w + C)[lane]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int i0 = 0; i0 < 64; i0 += 32) {
+                            const int i = i0 + lane;
+                            if (i < C) {
+                                if (act[0]) __stcs(reinterpret_cast<float*>(reinterpret_cast<char*>(gr0) + go) + i, w[i]);
+                                if (act[1]) __stcs(reinterpret_cast<float*>(reinterpret_cast<char*>(gr1) + go) + i, w[C + i]);
+                            }
+                        }
                     }
                 }
-            }
+            };
+            if (full) cells(IC<CH / NH>{}, hid, NH);
+            else if (hid == 0) cells(IC<1>{}, 0, 1);
+            arrive(&occ_free[nb & 1]);                   // cells are zero again (and my staged rows are complete)
+            if (full) stores(IC<CH / NH>{}, hid, NH);
+            else if (hid == 0) stores(IC<1>{}, 0, 1);
             __syncwarp();                                // staged rows have been read before the next chunk overwrites them
+            TT(5)                                        // helper bwd: gradient rows
         };
+        // Emission buffers in use while the lattice warp works on chunk j: j (being read), j + 1 (its gradient rows are
+        // next) and j - 1 (committed ahead, so that the lattice warp never waits for its emissions).
+        arrive(&eb_full[(nch - 1) % TNE]);               // the last chunk is still in its buffer from the forward sweep
         issue_rows(nch - 2);
+        issue_rows(nch - 3);
         for (int j = nch - 1; j >= 0; --j) {
-            if (j < nch - 1) {                           // the last chunk is still in its buffer from the forward sweep
-                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            if (j >= 1) {
+                asm volatile("cp.async.wait_group 1;" ::: "memory");   // rows(j - 1) have landed (j - 2 may be in flight)
                 __syncwarp();
-                commit_rows(j);
+                commit_rows(j - 1);                      // into the buffer chunk j + 2 has left (its gradient is done)
+                arrive(&eb_full[(j - 1) % TNE]);
             }
-            arrive(&eb_full[j % TNE]);
-            issue_rows(j - 2);
-            if (j < nch - 1) gradient_rows(j + 1, nch - 2 - j);
+            issue_rows(j - 3);
+            gradient_rows(j, nch - 1 - j);
         }
-        gradient_rows(0, nch - 1);
         asm volatile("cp.async.wait_all;" ::: "memory");
         if (lane == 0) meta[9 + hid] = (int)occ_hi;
+        if (hid == 0) { TT_FLUSH(16) }
         __syncthreads();                                 // (C) helpers' range checks are visible
         return;
     }
@@ -465,9 +519,11 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
         if (lane == 0) mbar_arrive(bar);
     };
 
+    TT_DECL
     auto fwd_chunk = [&](auto nfc, int j, int t0) {
         constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
+        TT(0)
         {
             bool ok[2];
             renorm_alpha<NSL>(a, ea, sca, lane, ok, p.strict_squash != 0, p.decay_max);
@@ -481,11 +537,14 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
             reinterpret_cast<int2*>(c + 64 * NSL)[lane] = make_int2(ea[0], ea[1]);
         }
         const int eb = (j % TNE) * (KF * RW);
+        TT(1)                                           // lattice fwd: renorm + ckpt store
         mbar_wait(&e_full[j % TNE], (ph_full >> (j % TNE)) & 1u);
         ph_full ^= 1u << (j % TNE);
+        TT(2)                                           // lattice fwd: wait e_full
 #pragma unroll
         for (int r = 0; r < NF; ++r) alpha_step<NSL>(a, sca, eb + r * RW, bl0, bl1, ep0, ep1, ma);
         arrive(&e_free[j % TNE]);
+        TT(3)                                           // lattice fwd: alpha steps
         const int tend = t0 + NF;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -553,8 +612,10 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
     };
     auto bwd_chunk = [&](auto nfc, int j, int t0, int nb) {
         constexpr int NF = decltype(nfc)::value;
+        TT(4)
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncwarp();
+        TT(5)                                           // lattice bwd: wait checkpoint
 #pragma unroll
         for (int q = 0; q < NSL; ++q) a[q] = reinterpret_cast<const float2*>(ckst)[q * 32 + lane];
         {
@@ -602,8 +663,10 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
             }
         }
         const int eb = (j % TNE) * (KF * RW);
+        TT(6)                                           // lattice bwd: take + bookkeeping
         mbar_wait(&eb_full[j % TNE], (ph_ebf >> (j % TNE)) & 1u);
         ph_ebf ^= 1u << (j % TNE);
+        TT(7)                                           // lattice bwd: wait eb_full
         float2 A[NF][NL];
 #pragma unroll
         for (int r = 0; r < NF; ++r) {
@@ -611,10 +674,12 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
 #pragma unroll
             for (int q = 0; q < NL; ++q) A[r][q] = a[2 * q + 1];
         }
+        TT(8)                                           // lattice bwd: alpha recompute
         if (nb >= 2) {                                  // the helpers have read (and zeroed) the cells of chunk nb - 2
             mbar_wait(&occ_free[nb & 1], (ph_ofree >> (nb & 1)) & 1u);
             ph_ofree ^= 1u << (nb & 1);
         }
+        TT(9)                                           // lattice bwd: wait occ_free
         const int ob = OCC_DELTA + (nb & 1) * (KF * RW);
 #pragma unroll
         for (int r = NF - 1; r >= 0; --r) {
@@ -628,6 +693,7 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
             }
         }
         arrive(&occ_full[nb & 1]);
+        TT(10)                                          // lattice bwd: beta + atomics
     };
     ckpt_issue(nch - 1);
     for (int j = nch - 1; j >= 0; --j) {
@@ -636,6 +702,7 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
         else bwd_chunk(IC<1>{}, j, t0, nch - 1 - j);
     }
     asm volatile("cp.async.wait_all;" ::: "memory");
+    TT_FLUSH(0)
     __syncthreads();                                     // (C)
     {
         constexpr unsigned OMAX = (unsigned)(8388608.0 * 1.002) + 8192u;
@@ -663,7 +730,7 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
 }
 
 template <int NSL, int NH, bool LOGITS, int CH, bool LIST>
-__global__ void __launch_bounds__(32 * (1 + NH)) ctc_team_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
+__global__ void __launch_bounds__(32 * (1 + NH), 2) ctc_team_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     extern __shared__ __align__(16) float team_smem[];
     if constexpr (!LIST) {
         ctc_team_body<NSL, NH, LOGITS, CH, false>(p, ckpt_ws, n_ckpt, blockIdx.x, blockIdx.x, p.B, team_smem, true);
@@ -692,13 +759,23 @@ int launch_team1(const CtcParams& p, float* ws, cudaStream_t st, int nblocks) {
 
 template <int NSL, bool LOGITS>
 int launch_team_nsl(const CtcParams& p, float* ws, cudaStream_t st, int ch, bool list, int nblocks) {
-    constexpr int NH = 3;
-    if (!list) return launch_team1<NSL, NH, LOGITS, KF, false>(p, ws, st, nblocks);
     (void)ch;
-    return launch_team1<NSL, NH, LOGITS, 2, true>(p, ws, st, nblocks);
+    if (!list) return launch_team1<NSL, 4, LOGITS, KF, false>(p, ws, st, nblocks);   // 8 frames per chunk, 4 helpers x 2 rows
+    return launch_team1<NSL, 2, LOGITS, 2, true>(p, ws, st, nblocks);                // 2 frames per chunk, 2 helpers x 1 row
 }
 
 }  // namespace
+
+#ifdef MDD_TEAM_TIMING
+extern "C" void mdd_debug_team_cycles(unsigned long long* out, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_team_cycles, sizeof(unsigned long long) * 32);
+    if (reset) {
+        unsigned long long z[32] = {0};
+        cudaMemcpyToSymbol(g_team_cycles, z, sizeof(z));
+    }
+}
+#endif
 
 bool ctc_team_supported(int C, int Lmax) { return C <= 63 && Lmax <= PGeo<8>::LCAP; }
 
