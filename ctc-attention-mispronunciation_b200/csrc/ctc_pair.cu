@@ -62,20 +62,23 @@ namespace {
 using namespace lattice;
 
 constexpr int RAWW = 132;                  // floats per staged pair row: 2*C log-probs (C <= 63) + 2 row-LSE + pad (16 B multiple)
-constexpr int NSLOT = 3;                   // staging slots: the chunk being consumed and two in flight
+// staging slots: the chunk being consumed and two in flight; the forward-only kernel (more warps per SM) keeps one in flight
+__host__ __device__ constexpr int nslot(int phase) { return phase == 1 ? 2 : 3; }
 
 struct PairSmem {
     int occ_off, rows_off, abuf_off, ckst_off, raw_off, total_floats;
 };
-__host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf) {
+__host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf, int phase = 0) {
     PairSmem s;
     int o = 0;
-    s.occ_off = o; o += KF * RW;                  // class occupancies of the chunk, fixed point (setup scratch too)
+    // class occupancies of the chunk, fixed point.  The setup tables (2*KF*RW ints) live in this block and the next;
+    // the forward-only kernel has no occupancies: its tables lie over the emission rows and the staging slots.
+    s.occ_off = o; if (phase != 1) o += KF * RW;
     s.rows_off = o; o += KF * RW;                 // exp(lp) rows of the current chunk, both utterances
-    s.abuf_off = o; if (!regbuf) o += KF * 32 * NSL;   // alpha label states of the chunk when they do not fit in registers
-    s.ckst_off = o; o += 32 * (2 * NSL + 2);      // the next checkpoint, landing by cp.async (backward sweep)
+    s.abuf_off = o; if (!regbuf && phase != 1) o += KF * 32 * NSL;   // alpha label states of the chunk when they do not fit in registers
+    s.ckst_off = o; if (phase != 1) o += 32 * (2 * NSL + 2);   // the next checkpoint, landing by cp.async (backward sweep)
     o = (o + 3) & ~3;
-    s.raw_off = o; o += NSLOT * KF * RAWW;        // log-prob rows as they arrive (class order); later the gradient rows
+    s.raw_off = o; o += nslot(phase) * KF * RAWW;  // log-prob rows as they arrive (class order); later the gradient rows
     s.total_floats = (o + 3) & ~3;
     return s;
 }
@@ -85,7 +88,10 @@ __host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf) {
 // range per frame for about twice the time per frame, in front of the log-space kernel.
 // One pair of utterances, start to finish.  `pair` selects the utterances (2*pair, 2*pair+1 of the batch, or of the
 // compacted list), `slot` the checkpoint block of the workspace this warp may use.
-template <int NSL, bool REGBUF, bool LOGITS, int CH, bool LIST>
+// PHASE 0: both sweeps in one kernel.  PHASE 1: the forward sweep alone (loss, checkpoints, a record of P per
+// utterance) -- it needs a third of the registers, so two to three times as many warps share an SM; PHASE 2: the
+// backward sweep alone, from the checkpoints and the record.
+template <int NSL, bool REGBUF, bool LOGITS, int CH, bool LIST, int PHASE = 0>
 __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restrict__ ckpt_ws, int n_ckpt, int pair,
                                               int slot, int n_utt) {
     using G = PGeo<NSL>;
@@ -94,7 +100,8 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     extern __shared__ __align__(16) float smem_f[];
-    const PairSmem lay = pair_smem_layout(NSL, REGBUF);
+    constexpr int NSLOT = nslot(PHASE);
+    const PairSmem lay = pair_smem_layout(NSL, REGBUF, PHASE);
     float* base = smem_f + (size_t)warp * lay.total_floats;
     unsigned* occ = reinterpret_cast<unsigned*>(base + lay.occ_off);   // [KF][RW], laid out like the emission rows
     float* rows = base + lay.rows_off;                           // [KF][RW]
@@ -113,6 +120,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     int* lab = scratch;
     int* hist = scratch + 512;
     static_assert(2 * KF * RW >= 1280 + 288 + 128, "setup scratch must fit in the occupancy + emission rows");
+    static_assert(KF * RW + 2 * KF * RAWW >= 2 * KF * RW, "forward-only kernel: setup scratch over the rows + staging slots");
     static_assert(512 + 144 <= 1280, "label histogram [2][72] behind the labels");
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -282,7 +290,8 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     const bool isb10 = ov[1][0] && oc[1][0] == blank, isb11 = ov[1][1] && oc[1][1] == blank;
     __syncwarp();
     // the occupancy cells start at zero; zero pads of the staged rows (emission of unused label slots)
-    for (int i = lane; i < KF * RW; i += 32) occ[i] = 0u;
+    if constexpr (PHASE != 1)
+        for (int i = lane; i < KF * RW; i += 32) occ[i] = 0u;
     if (lane < KF) {
         rows[lane * RW + zslot0] = 0.f;
         rows[lane * RW + zslot1] = 0.f;
@@ -431,9 +440,11 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     int koff[2] = {0, 0};
     float* ck = ckpt_ws + (size_t)slot * n_ckpt * CKW;
 
-    issue_rows(0);
-    issue_rows(1);
-    if (want_grad) {                                    // rows t >= T_max of the gradient are zero (torch semantics)
+    if constexpr (PHASE != 2) {
+        issue_rows(0);
+        if constexpr (NSLOT == 3) issue_rows(1);
+    }
+    if (want_grad && PHASE != 1) {                      // rows t >= T_max of the gradient are zero (torch semantics)
         for (int t = Tmax; t < T; ++t)
             for (int i = lane; i < C; i += 32) {
                 if (act[0]) __stcs(gr0 + (size_t)t * gstride + i, 0.f);
@@ -444,11 +455,12 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     auto fwd_chunk = [&](auto nfc, int j, int t0) {
         constexpr int NF = decltype(nfc)::value;
         const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
-        asm volatile("cp.async.wait_group 1;" ::: "memory");     // rows of chunk j have landed (j + 1 may be in flight)
+        if constexpr (NSLOT == 3) asm volatile("cp.async.wait_group 1;" ::: "memory");   // rows of chunk j have landed (j + 1 may be in flight)
+        else asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncwarp();
         commit_rows(nfc, j, kill0, kill1);
         __syncwarp();
-        issue_rows(j + 2);                              // into the slot chunk j - 1 was consumed from
+        issue_rows(j + NSLOT - 1);                      // into the slot chunk j - 1 was consumed from
         {
             bool ok[2];
             renorm_alpha<NSL>(a, ea, sca, lane, ok, p.strict_squash != 0, p.decay_max);
@@ -496,12 +508,33 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
             }
         }
     };
-    for (int j = 0; j < nch; ++j) {
-        int t0;
-        if (chunk_geom(j, t0)) fwd_chunk(IC<CH>{}, j, t0);
-        else fwd_chunk(IC<1>{}, j, t0);
+    if constexpr (PHASE != 2) {
+        for (int j = 0; j < nch; ++j) {
+            int t0;
+            if (chunk_geom(j, t0)) fwd_chunk(IC<CH>{}, j, t0);
+            else fwd_chunk(IC<1>{}, j, t0);
+        }
+        asm volatile("cp.async.wait_all;" ::: "memory");
     }
-    asm volatile("cp.async.wait_all;" ::: "memory");
+    if constexpr (PHASE == 1) {                         // hand P over to the backward kernel: 1 / mantissa, exponent, flag
+        if (want_grad && lane == 0) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                if (act[h]) p.rec[bidx[h]] = make_float4(zi[h], __int_as_float(koff[h]), __int_as_float(flag[h]), 0.f);
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (act[h] && lane == 0 && (!want_grad || flag[h])) p.flags[bidx[h]] = flag[h];
+        return;
+    }
+    if constexpr (PHASE == 2) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (act[h]) {
+                const float4 r = p.rec[bidx[h]];
+                zi[h] = r.x; koff[h] = __float_as_int(r.y); flag[h] = __float_as_int(r.z);
+            }
+    }
     if (!want_grad || ((flag[0] || !act[0]) && (flag[1] || !act[1]))) {
 #pragma unroll
         for (int h = 0; h < 2; ++h)
@@ -552,7 +585,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         asm volatile("cp.async.wait_group 1;" ::: "memory");
         __syncwarp();
         ckpt_take();
-        if (j < nch - 1) commit_rows(nfc, j, kill0, kill1);       // the last chunk is still staged (and exponentiated)
+        if (PHASE == 2 || j < nch - 1) commit_rows(nfc, j, kill0, kill1);   // (one kernel: the last chunk is still staged)
         __syncwarp();
         ckpt_issue(j - 1);                              // the staging block has been read
         // a / ea hold the checkpoint of this chunk: boundary factors and the beta exponents that go with it
@@ -686,8 +719,9 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         }
     };
 
-    // in flight when chunk j starts, oldest first: rows(j), checkpoint(j), rows(j - 1); the last chunk's rows are
-    // still staged from the forward sweep
+    // in flight when chunk j starts, oldest first: rows(j), checkpoint(j), rows(j - 1); in the single kernel the last
+    // chunk's rows are still staged from the forward sweep
+    if constexpr (PHASE == 2) issue_rows(nch - 1);
     ckpt_issue(nch - 1);
     issue_rows(nch - 2);
     for (int j = nch - 1; j >= 0; --j) {
@@ -727,12 +761,12 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     }
 }
 
-template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST>
+template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST, int PHASE = 0>
 __global__ void __maxnreg__(MAXR)
 ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if constexpr (!LIST) {
-        if (w < ((p.B + 1) >> 1)) ctc_pair_body<NSL, REGBUF, LOGITS, CH, false>(p, ckpt_ws, n_ckpt, w, w, p.B);
+        if (w < ((p.B + 1) >> 1)) ctc_pair_body<NSL, REGBUF, LOGITS, CH, false, PHASE>(p, ckpt_ws, n_ckpt, w, w, p.B);
     } else {
         // second tier: this warp owns checkpoint block w and walks the pairs w, w + #warps, ... of the flagged list
         const int n_utt = *p.list_count, stride = gridDim.x * (blockDim.x >> 5);
@@ -785,9 +819,9 @@ __global__ void __launch_bounds__(1024) compact_flagged_kernel(const int32_t* __
     if (tid == 0) *count = base;
 }
 
-template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST>
+template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST, int PHASE = 0>
 int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st, int npairs) {
-    const PairSmem lay = pair_smem_layout(NSL, REGBUF);
+    const PairSmem lay = pair_smem_layout(NSL, REGBUF, PHASE);
     size_t smem = (size_t)lay.total_floats * 4;                  // one warp (= one pair) per CTA
     // Warps per SM: the register file allows 8; fewer when that packs the pairs into full waves (a pair runs for the
     // whole kernel, so 13.8 pairs per SM are better served by 7 warps x 2 waves than by 8 + 5.8).
@@ -795,8 +829,9 @@ int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st, int npairs) {
     int wps = wps_env;
     if (wps <= 0) {
         double best = 0.0;
-        const int wmax = 65536 / (32 * ((MAXR + 7) & ~7));       // register file
-        for (int w = wmax; w >= wmax - 2; --w) {
+        int wmax = 65536 / (32 * ((MAXR + 7) & ~7));             // register file
+        wmax = std::min(wmax, (int)((227 * 1024) / (smem + 1024)));   // shared memory
+        for (int w = wmax; w >= std::max(1, wmax - 2); --w) {
             const long long slots = (long long)kNumSM * w;
             const double eff = (double)npairs / (double)(((npairs + slots - 1) / slots) * slots);
             if (eff > best + 0.04) { best = eff; wps = w; }
@@ -806,17 +841,13 @@ int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st, int npairs) {
         const size_t want = ((233472 / (size_t)wps) - 1024 - 64) & ~(size_t)15;
         if (want > smem && want <= 227 * 1024) smem = want;
     }
-    static size_t configured = 0;
-    if (configured < smem) {
-        if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)smem) != cudaSuccess) {
-            cudaGetLastError();
-            return MDD_E_CUDA;
-        }
-        configured = smem;
+    if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST, PHASE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)smem) != cudaSuccess) {                // per device: set on every call (cheap)
+        cudaGetLastError();
+        return MDD_E_CUDA;
     }
     const int n_ckpt = p.T / CH + 2 * CH;
-    ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
+    ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST, PHASE><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
     MDD_CHECK_LAUNCH();
     return MDD_OK;
 }
@@ -830,8 +861,14 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
     static int team_max = env_int("MDD_CTC_TEAM_MAX_PAIRS", 2 * kNumSM);
     const bool team_ok = ctc_team_supported(p.C, p.Lmax);
     int rc;
+    static int split = env_int("MDD_CTC_SPLIT", 1);
+    p.rec = reinterpret_cast<float4*>(ws + (size_t)npairs * (p.T / KF + 2 * KF) * PGeo<NSL>::CKW);
     if (team_ok && npairs <= team_max) rc = launch_ctc_team(p, ws, st, false, npairs);
-    else rc = launch_cfg1<NSL, REGBUF, MAXR, LOGITS, KF, false>(p, ws, st, npairs);
+    else if (split || !p.grad) {
+        // forward sweep at high occupancy (a third of the registers), then the backward sweep from its checkpoints
+        rc = launch_cfg1<NSL, REGBUF, 128, LOGITS, KF, false, 1>(p, ws, st, npairs);
+        if (!rc && p.grad) rc = launch_cfg1<NSL, REGBUF, MAXR, LOGITS, KF, false, 2>(p, ws, st, npairs);
+    } else rc = launch_cfg1<NSL, REGBUF, MAXR, LOGITS, KF, false>(p, ws, st, npairs);
     if (rc || !p.list) return rc;
     // second tier: the flagged utterances again, renormalised every CH2 frames, in the same checkpoint workspace
     const size_t ws_floats = (size_t)npairs * (p.T / KF + 2 * KF) * PGeo<NSL>::CKW;
@@ -879,7 +916,7 @@ size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
     const int nsl = pick_nsl(Lmax);
     if (!nsl) return 0;
     const size_t n_ckpt = (size_t)T / KF + 2 * KF;
-    return (size_t)((B + 1) / 2) * n_ckpt * 32 * (2 * nsl + 2) * 4;
+    return (size_t)((B + 1) / 2) * n_ckpt * 32 * (2 * nsl + 2) * 4 + ((size_t)B + 2) * 16;   // + one record per utterance
 }
 #endif
 

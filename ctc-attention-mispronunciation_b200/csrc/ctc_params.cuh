@@ -37,6 +37,7 @@ struct CtcParams {
     int32_t* list_count;
     int list_cap_pairs;
     int decay_max;            // largest per-chunk decay (bits) of the lanes holding the bulk of alpha
+    float4* rec;              // [B] forward kernel -> backward kernel: 1 / mantissa(P), exponent, flag
 };
 
 // fp64 linear-domain kernel, one CTA per utterance (ctc_exact.cu): robust path and per-utterance fallback
