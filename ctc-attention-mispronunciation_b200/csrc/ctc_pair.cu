@@ -770,6 +770,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     } else {
         // second tier: this warp owns checkpoint block w and walks the pairs w, w + #warps, ... of the flagged list
         const int n_utt = *p.list_count, stride = gridDim.x * (blockDim.x >> 5);
+        if (n_utt <= p.list_team_max) return;                    // few flagged utterances: the team kernel has taken them
         for (int pr = w; 2 * pr < n_utt; pr += stride) {
             ctc_pair_body<NSL, REGBUF, LOGITS, CH, true>(p, ckpt_ws, n_ckpt, pr, w, n_utt);
             asm volatile("cp.async.wait_all;" ::: "memory");
@@ -878,8 +879,15 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
     compact_flagged_kernel<<<1, 1024, 0, st>>>(p.flags, p.B, p.list, p.list_count);
     MDD_CHECK_LAUNCH();
     p.list_cap_pairs = cap;
+    // Few flagged utterances: one CTA per pair with helper warps (each pair alone on its SM would crawl in the pair
+    // kernel); many: the pair kernel's own occupancy wins.  The count is on the device, so both are launched and each
+    // leaves at once when the other is in charge.
     static int team_tier2 = env_int("MDD_CTC_TEAM_TIER2", 1);
-    if (team_ok && team_tier2) return launch_ctc_team(p, ws, st, true, std::min(cap, 2 * sm_count()));
+    p.list_team_max = (team_ok && team_tier2) ? 2 * std::min(cap, 2 * sm_count()) : 0;
+    if (p.list_team_max > 0) {
+        rc = launch_ctc_team(p, ws, st, true, std::min(cap, 2 * sm_count()));
+        if (rc) return rc;
+    }
     return launch_cfg1<NSL, REGBUF, MAXR, LOGITS, CH2, true>(p, ws, st, cap);
 }
 

@@ -36,6 +36,7 @@ struct CtcParams {
     int32_t* list;
     int32_t* list_count;
     int list_cap_pairs;
+    int list_team_max;        // second tier: up to this many flagged utterances go to the team kernel, more to the pair kernel
     int decay_max;            // largest per-chunk decay (bits) of the lanes holding the bulk of alpha
     float4* rec;              // [B] forward kernel -> backward kernel: 1 / mantissa(P), exponent, flag
 };

@@ -737,6 +737,7 @@ __global__ void __launch_bounds__(32 * (1 + NH), 2) ctc_team_kernel(CtcParams p,
     } else {
         // the flagged utterances: this CTA owns checkpoint block blockIdx.x and walks the pairs blockIdx.x, + grid, ...
         const int n_utt = *p.list_count;
+        if (n_utt > p.list_team_max) return;                     // many flagged utterances: the pair kernel's second tier takes them
         for (int pr = blockIdx.x; 2 * pr < n_utt; pr += gridDim.x)
             ctc_team_body<NSL, NH, LOGITS, CH, true>(p, ckpt_ws, n_ckpt, pr, blockIdx.x, n_utt, team_smem, pr == (int)blockIdx.x);
     }

@@ -822,6 +822,62 @@ def test_config1_words_end_to_end(M):
             assert got[b][k] == want[k], (js["words"][b], k)
 
 
+def test_config5_ragged_greedy_mdd_pipeline_vs_oracle(M, vocab43):
+    """BASELINE config 5 as a config: a ragged batch (T 50..1500, 2048 utterances, C = 43 with 'sil' and 'err' among the
+    classes), dealt to 8 ranks by mddctc.dist.balanced_buckets; every rank's share goes through greedy decode ->
+    sil/err filtering -> Levenshtein alignment -> MDD post-processing on the device and must equal the CPU oracle
+    (decoded tokens, distance, op path, aligned rows, fault lists, counts) for every utterance."""
+    from mddctc.decoder import GreedyDecoder
+    from mddctc.dist import balanced_buckets
+    from mddctc.mdd import MDDScorer
+    g = torch.Generator().manual_seed(505)
+    B, T, C, Lc, world = 2048, 1500, 43, 188, 8
+    lens = torch.randint(50, T + 1, (B,), generator=g)
+    shards = balanced_buckets(lens.tolist(), world)
+    assert sorted(i for s in shards for i in s) == list(range(B))
+    frames = [int(lens[s].sum()) for s in shards]
+    assert max(frames) - min(frames) <= T                         # equal work to within one utterance
+    gd = GreedyDecoder(vocab43, space_idx=-1, blank_index=0)
+    sc = MDDScorer(vocab43)
+    wid = O.word_ids(vocab43)
+    checked = 0
+    for rank in (0, 5):                                           # two of the eight shares, every utterance of each
+        idx = torch.tensor(shards[rank])
+        ln = lens[idx]
+        Bs = len(idx)
+        gg = torch.Generator().manual_seed(1000 + rank)
+        x = torch.randn(T, Bs, C, generator=gg)
+        x.scatter_add_(2, torch.randint(0, C, (T, Bs, 1), generator=gg), torch.full((T, Bs, 1), 4.0))
+        lp = torch.log_softmax(x, -1)
+        can = torch.randint(1, C, (Bs, Lc), generator=gg, dtype=torch.int32)        # 'sil' (2) and 'err' (42) occur
+        can_len = torch.clamp((ln + 7) // 8, max=Lc).to(torch.int32)
+        tokens, out_len, _ = gd.decode_tokens(lp.cuda(), ln.cuda())
+        r = sc.align_tokens(tokens, out_len, can.cuda(), can_len.cuda(), max_dec=T, max_can=Lc)
+        got = sc.to_python(r)
+        wt, wl, _ = O.greedy_tokens(lp.numpy(), ln.numpy(), 0, wid)
+        tk, ol = tokens.cpu().numpy(), out_len.cpu().numpy()
+        assert ol.tolist() == wl.tolist()
+        dec = [[int(sc.dec_map[k]) for k in wt[b, :wl[b]] if sc.dec_map[k] >= 0] for b in range(Bs)]
+        cn = [[int(sc.can_map[k]) for k in can[b, :can_len[b]].tolist() if sc.can_map[k] >= 0] for b in range(Bs)]
+        dist, paths, st = O.edit_align(dec, cn)
+        for b in range(Bs):
+            assert tk[b, :ol[b]].tolist() == wt[b, :wl[b]].tolist()
+            if st[b]:
+                assert isinstance(got[b], TypeError)
+                continue
+            w = O.mdd_post(dec[b], cn[b], paths[b])
+            gb = got[b]
+            assert gb["dist"] == int(dist[b]) and gb["path0"] == paths[b]
+            name = sc.name
+            assert gb["dec"] == [name(k) for k in w["dec"]] and gb["can"] == [name(k) for k in w["can"]]
+            assert gb["path"] == w["ops"]
+            assert gb["ins"] == [name(k) for k in w["ins"]] and gb["sub"] == [name(k) for k in w["sub"]]
+            assert gb["del"] == [name(k) for k in w["del"]]
+            assert (gb["correct"], gb["del_sub"]) == (w["correct"], w["del_sub"])
+            checked += 1
+    assert checked > 400
+
+
 # ----------------------------------------------------------------------------------------------------- prefix scorer
 def test_prefix_scorer_vs_oracle_and_invariant(M):
     from mddctc.prefix import CTCPrefixScorer
