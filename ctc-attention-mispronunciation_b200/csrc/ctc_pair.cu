@@ -401,27 +401,39 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         const float* slot = raw + (j % NSLOT) * (KF * RAWW);
         auto body = [&](auto killc) {
             constexpr bool KILL = decltype(killc)::value != 0;
+            // rows in batches of up to four: all of a batch's loads are issued before the first exponential, so that
+            // a batch costs one shared-memory latency instead of one per row
+            constexpr int RB = NF < 4 ? NF : 4;
 #pragma unroll
-            for (int r = 0; r < NF; ++r) {
-                const float* s = slot + r * RAWW;
-                float2 v0, v1;
-                if constexpr (LOGITS) {
-                    const float n0 = s[2 * C] * -LOG2E, n1 = s[2 * C + 1] * -LOG2E;
-                    v0 = make_float2(fast_exp2(fmaf(s[ro00], LOG2E, n0)), fast_exp2(fmaf(s[ro01], LOG2E, n0)));
-                    v1 = make_float2(fast_exp2(fmaf(s[ro10], LOG2E, n1)), fast_exp2(fmaf(s[ro11], LOG2E, n1)));
-                } else {
-                    v0 = make_float2(fast_exp(s[ro00]), fast_exp(s[ro01]));
-                    v1 = make_float2(fast_exp(s[ro10]), fast_exp(s[ro11]));
+            for (int r0 = 0; r0 < NF; r0 += RB) {
+                float x[RB][4], nl[RB][2];
+#pragma unroll
+                for (int i = 0; i < RB; ++i) {
+                    const float* s = slot + (r0 + i) * RAWW;
+                    x[i][0] = s[ro00]; x[i][1] = s[ro01]; x[i][2] = s[ro10]; x[i][3] = s[ro11];
+                    if constexpr (LOGITS) { nl[i][0] = s[2 * C]; nl[i][1] = s[2 * C + 1]; }
                 }
-                if constexpr (KILL) {
-                    if (kill0) v0 = make_float2(0.f, 0.f);
-                    if (kill1) v1 = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int i = 0; i < RB; ++i) {
+                    float2 v0, v1;
+                    if constexpr (LOGITS) {
+                        const float n0 = nl[i][0] * -LOG2E, n1 = nl[i][1] * -LOG2E;
+                        v0 = make_float2(fast_exp2(fmaf(x[i][0], LOG2E, n0)), fast_exp2(fmaf(x[i][1], LOG2E, n0)));
+                        v1 = make_float2(fast_exp2(fmaf(x[i][2], LOG2E, n1)), fast_exp2(fmaf(x[i][3], LOG2E, n1)));
+                    } else {
+                        v0 = make_float2(fast_exp(x[i][0]), fast_exp(x[i][1]));
+                        v1 = make_float2(fast_exp(x[i][2]), fast_exp(x[i][3]));
+                    }
+                    if constexpr (KILL) {
+                        if (kill0) v0 = make_float2(0.f, 0.f);
+                        if (kill1) v1 = make_float2(0.f, 0.f);
+                    }
+                    float* d = rows + (r0 + i) * RW;
+                    d[wp[0]] = v0.x;
+                    d[wp[1]] = v0.y;
+                    d[wp[2]] = v1.x;
+                    d[wp[3]] = v1.y;
                 }
-                float* d = rows + r * RW;
-                d[wp[0]] = v0.x;
-                d[wp[1]] = v0.y;
-                d[wp[2]] = v1.x;
-                d[wp[3]] = v1.y;
             }
         };
         if (kill0 || kill1) body(IC<1>{});
@@ -665,6 +677,22 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
             const float og0 = g0 * (1.f / FIX), og1 = g1 * (1.f / FIX);
             float* gs = raw + (j % NSLOT) * (KF * RAWW);
             constexpr int fixi = (int)FIX;
+#ifndef MDD_PAIR_DIRECT_GRAD
+#define MDD_PAIR_DIRECT_GRAD 1
+#endif
+            // Where my four values of a row go.  Direct: straight to the gradient array, four 4-byte streaming stores per
+            // row (every float of the pair's row is written by exactly one lane; the sectors fill up in L2) -- the
+            // shared-memory pipe is this kernel's bound, and staging the row for wide stores costs it 9 wavefronts a frame.
+            constexpr bool DIRECT = MDD_PAIR_DIRECT_GRAD != 0;
+            char* dq[4];
+            if constexpr (DIRECT) {
+                const unsigned long long go = (unsigned long long)(unsigned)t0 * gstride_b;
+                dq[0] = reinterpret_cast<char*>(gr0 + oc[0][0]) + go;
+                dq[1] = reinterpret_cast<char*>(gr0 + oc[0][1]) + go;
+                dq[2] = reinterpret_cast<char*>(gr1 + oc[1][0]) + go;
+                dq[3] = reinterpret_cast<char*>(gr1 + oc[1][1]) + go;
+            }
+            const bool sv0 = act[0] && ov[0][0], sv1 = act[0] && ov[0][1], sv2 = act[1] && ov[1][0], sv3 = act[1] && ov[1][1];
             // one row ahead: cells and their warp totals (REDUX) of row r + 1 are on their way while row r is finished
             int oc4[4], on4[4] = {0, 0, 0, 0}, ts0, ts1, tn0 = 0, tn1 = 0;
             auto cells = [&](int r, int (&o)[4], int& s0, int& s1) {
@@ -689,17 +717,29 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
                 if (isb11) oc4[3] = fixi - ts1;
                 // every row total must be a fraction of Z in [0, 1] up to rounding: catches overflow / NaN upstream
                 occ_hi = max(occ_hi, max((unsigned)(ts0 + 8192), (unsigned)(ts1 + 8192)));
-                float* w = gs + r * RAWW;
-                w[wg[0]] = fmaf(-(float)oc4[0], og0, pv0.x * g0);
-                w[wg[1]] = fmaf(-(float)oc4[1], og0, pv0.y * g0);
-                w[wg[2]] = fmaf(-(float)oc4[2], og1, pv1.x * g1);
-                w[wg[3]] = fmaf(-(float)oc4[3], og1, pv1.y * g1);
+                const float v0 = fmaf(-(float)oc4[0], og0, pv0.x * g0), v1 = fmaf(-(float)oc4[1], og0, pv0.y * g0);
+                const float v2 = fmaf(-(float)oc4[2], og1, pv1.x * g1), v3 = fmaf(-(float)oc4[3], og1, pv1.y * g1);
+                if constexpr (DIRECT) {
+                    if (sv0) __stcs(reinterpret_cast<float*>(dq[0]), v0);
+                    if (sv1) __stcs(reinterpret_cast<float*>(dq[1]), v1);
+                    if (sv2) __stcs(reinterpret_cast<float*>(dq[2]), v2);
+                    if (sv3) __stcs(reinterpret_cast<float*>(dq[3]), v3);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) dq[k] += gstride_b;
+                } else {
+                    float* w = gs + r * RAWW;
+                    w[wg[0]] = v0;
+                    w[wg[1]] = v1;
+                    w[wg[2]] = v2;
+                    w[wg[3]] = v3;
+                }
 #pragma unroll
                 for (int k = 0; k < 4; ++k) oc4[k] = on4[k];
                 ts0 = tn0; ts1 = tn1;
             }
             __syncwarp();
-            if (gvec) {                                 // the pair's two rows are one 16-byte aligned run of 2*C floats
+            if constexpr (DIRECT) {
+            } else if (gvec) {                                 // the pair's two rows are one 16-byte aligned run of 2*C floats
                 char* gq = reinterpret_cast<char*>(gr0) + (unsigned long long)(unsigned)t0 * gstride_b + lane * 16;
 #pragma unroll
                 for (int r = 0; r < NF; ++r) {
