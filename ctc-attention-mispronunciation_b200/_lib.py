@@ -95,7 +95,7 @@ class PostOut(C.Structure):
 EXPORTS = ["mdd_version", "mdd_error_string", "mdd_launch_count", "mdd_launch_count_reset",
            "mdd_ctc_loss_workspace_bytes", "mdd_ctc_loss", "mdd_ctc_loss_logits", "mdd_row_lse", "mdd_copy_h2d_2d", "mdd_ctc_scale_grad", "mdd_greedy_decode", "mdd_collapse", "mdd_post_align", "mdd_corpus_counts",
            "mdd_edit_align_workspace_bytes", "mdd_edit_align", "mdd_beam_search_workspace_bytes", "mdd_beam_search",
-           "mdd_exp_transpose", "mdd_prefix_init", "mdd_prefix_score", "mdd_prefix_advance", "mdd_prefix_select"]
+           "mdd_exp_transpose", "mdd_prefix_init", "mdd_prefix_probs", "mdd_prefix_score", "mdd_prefix_advance", "mdd_prefix_select"]
 
 
 def lib():
@@ -135,6 +135,7 @@ def lib():
     L.mdd_beam_search.argtypes = [vp, i, i, i, vp, i, i, vp, d, vp, i, vp, vp, vp, vp, sz, vp]
     L.mdd_exp_transpose.argtypes = [vp, i, i, i, vp, vp]
     L.mdd_prefix_init.argtypes = [vp, i, i, i, vp, i, i, vp, vp]
+    L.mdd_prefix_probs.argtypes = [vp, i, i, i, vp, vp]
     L.mdd_prefix_score.argtypes = [vp, i, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, vp]
     L.mdd_prefix_advance.argtypes = [vp, i, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, vp, vp]
     L.mdd_prefix_select.argtypes = [i, i, i, i, i, d, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]

@@ -2,14 +2,15 @@
 
 The reference has no attention decoder and no such function; its nearest code is the (prBlank, prNonBlank, prTotal)
 recursion and the sort + [:beamWidth] of egs/attention_aug/utils/BeamSearch.py:52-66,99-125.  This module provides the
-standard Watanabe/ESPnet-style scorer on the CUDA kernels (mdd_prefix_init / mdd_prefix_score / mdd_prefix_select /
-mdd_prefix_advance) and the label-synchronous joint beam search that fuses it with externally supplied attention
+standard Watanabe/ESPnet-style scorer on the CUDA kernels (mdd_prefix_probs / mdd_prefix_init / mdd_prefix_score /
+mdd_prefix_select / mdd_prefix_advance) and the label-synchronous joint beam search that fuses it with externally supplied attention
 log-probabilities:
 
     score(g.c) = score(g) + ctc_weight * (psi(g.c) - psi(g)) + (1 - ctc_weight) * att_logp[c]
 
 Scores and CTC state are fp64 on the device (see csrc/prefix_score.cu); a decoding step is three kernel launches
-(score, select, advance) and whatever the caller's attention decoder does -- no torch.topk / gather in between.
+(score, select, advance) and whatever the caller's attention decoder does -- no torch.topk / gather in between, and
+joint_beam_search allocates its beam buffers once (two state sets used in turn), not per step.
 """
 from __future__ import annotations
 
@@ -30,6 +31,10 @@ class CTCPrefixScorer:
         self.blank = blank
         self.lens = None if input_lengths is None else input_lengths.to(device=self.dev, dtype=torch.int64).contiguous()
         self._L = _lib.lib()
+        # emission probabilities in fp64, utterance-major, exponentiated once for all the decoding steps
+        self.p_lin = torch.empty((self.B, self.T, self.C), dtype=torch.float64, device=self.dev)
+        _lib.check(self._L.mdd_prefix_probs(self.x.data_ptr(), self.T, self.B, self.C, self.p_lin.data_ptr(),
+                                            _rt.stream_ptr(self.dev)), "mdd_prefix_probs")
 
     def initial_state(self, max_len=None, all_slots_live=False):
         """The empty prefix.  By default only slot 0 of every utterance is live (a beam search starts from ONE empty
@@ -48,29 +53,38 @@ class CTCPrefixScorer:
                 "score": score, "flag": flag,
                 "tokens": torch.full((B, W, max_len or T), -1, dtype=torch.int32, device=dev)}
 
-    def score(self, state):
+    def empty_state(self, like):
+        """Uninitialised buffers shaped like ``like`` (the second state set of a beam search)."""
+        return {k: torch.empty_like(v) for k, v in like.items()}
+
+    def score(self, state, out=None):
         """psi[B,W,C] = log p_ctc(g.c, ...) for every candidate label, psi_eos[B,W] = log p_ctc(g) (fp64).
-        Finished / dead hypotheses are not extended (all -inf)."""
-        psi = torch.empty((self.B, self.W, self.C), dtype=torch.float64, device=self.dev)
-        eos = torch.empty((self.B, self.W), dtype=torch.float64, device=self.dev)
-        _lib.check(self._L.mdd_prefix_score(self.x.data_ptr(), self.T, self.B, self.C, _rt.ptr(self.lens), self.blank,
-                                            self.W, state["r"].data_ptr(), state["last"].data_ptr(),
+        Finished / dead hypotheses are not extended (all -inf).  ``out`` = (psi, psi_eos) buffers to reuse."""
+        if out is None:
+            out = (torch.empty((self.B, self.W, self.C), dtype=torch.float64, device=self.dev),
+                   torch.empty((self.B, self.W), dtype=torch.float64, device=self.dev))
+        psi, eos = out
+        _lib.check(self._L.mdd_prefix_score(self.p_lin.data_ptr(), self.T, self.B, self.C, _rt.ptr(self.lens),
+                                            self.blank, self.W, state["r"].data_ptr(), state["last"].data_ptr(),
                                             state["glen"].data_ptr(), state["flag"].data_ptr(), psi.data_ptr(),
                                             eos.data_ptr(), _rt.stream_ptr(self.dev)), "mdd_prefix_score")
         return psi, eos
 
-    def select(self, state, psi, psi_eos, att_logp, ctc_weight=0.3, eos=None):
+    def select(self, state, psi, psi_eos, att_logp, ctc_weight=0.3, eos=None, out=None):
         """One beam step: the W best of the W*C candidates of every utterance.  Returns the new state WITHOUT its CTC
-        recursion state (call advance) plus (sel_hyp, sel_label)."""
+        recursion state (call advance and store the result under "r") plus (sel_hyp, sel_label).  ``out`` = a state
+        dict whose buffers are overwritten (its "r" is left alone)."""
         B, W, C, dev = self.B, self.W, self.C, self.dev
-        att = att_logp.to(device=dev, dtype=torch.float32).contiguous()
+        att = att_logp
+        if att.dtype != torch.float32 or att.device != dev or not att.is_contiguous():
+            att = att.to(device=dev, dtype=torch.float32).contiguous()
         if tuple(att.shape) != (B, W, C):
             raise RuntimeError("att_logp must be (B, W, C)")
         max_len = state["tokens"].shape[2]
-        new = {"last": torch.empty_like(state["last"]), "glen": torch.empty_like(state["glen"]),
-               "psi": torch.empty_like(state["psi"]), "score": torch.empty_like(state["score"]),
-               "flag": torch.empty_like(state["flag"]), "tokens": torch.empty_like(state["tokens"])}
-        sel_hyp = torch.empty((B, W), dtype=torch.int32, device=dev)
+        new = out if out is not None else self.empty_state({k: v for k, v in state.items() if k not in ("r", "sel_hyp")})
+        if "sel_hyp" not in new:
+            new["sel_hyp"] = torch.empty((B, W), dtype=torch.int32, device=dev)
+        sel_hyp = new["sel_hyp"]
         rc = self._L.mdd_prefix_select(B, W, C, self.blank, -1 if eos is None else int(eos), float(ctc_weight), max_len,
                                        psi.data_ptr(), psi_eos.data_ptr(), att.data_ptr(), state["score"].data_ptr(),
                                        state["psi"].data_ptr(), state["glen"].data_ptr(), state["flag"].data_ptr(),
@@ -80,14 +94,14 @@ class CTCPrefixScorer:
         _lib.check(rc, "mdd_prefix_select")
         return new, sel_hyp, new["last"]
 
-    def advance(self, state, sel_hyp, sel_label, new_flag=None):
+    def advance(self, state, sel_hyp, sel_label, new_flag=None, out=None):
         """CTC recursion state r (B,W,T,2) of the chosen (parent hypothesis, label) pairs; slots whose new flag is
-        non-zero (finished / dead) or whose parent is -1 are left untouched."""
+        non-zero (finished / dead) or whose parent is -1 are left untouched.  ``out`` = the buffer to write."""
         sel_hyp = sel_hyp.to(device=self.dev, dtype=torch.int32).contiguous()
         sel_label = sel_label.to(device=self.dev, dtype=torch.int32).contiguous()
-        r_new = torch.empty_like(state["r"])
-        _lib.check(self._L.mdd_prefix_advance(self.x.data_ptr(), self.T, self.B, self.C, _rt.ptr(self.lens), self.blank,
-                                              self.W, state["r"].data_ptr(), state["last"].data_ptr(),
+        r_new = out if out is not None else torch.empty_like(state["r"])
+        _lib.check(self._L.mdd_prefix_advance(self.p_lin.data_ptr(), self.T, self.B, self.C, _rt.ptr(self.lens),
+                                              self.blank, self.W, state["r"].data_ptr(), state["last"].data_ptr(),
                                               state["glen"].data_ptr(), sel_hyp.data_ptr(), sel_label.data_ptr(),
                                               _rt.ptr(new_flag), r_new.data_ptr(), _rt.stream_ptr(self.dev)),
                    "mdd_prefix_advance")
@@ -122,10 +136,14 @@ def joint_beam_search(log_probs, input_lengths, att_logp_fn, beam=10, ctc_weight
     scorer = CTCPrefixScorer(log_probs, input_lengths, blank=blank, beam=beam)
     max_len = max_len or scorer.T
     state = scorer.initial_state(max_len=max_len)
+    state["sel_hyp"] = torch.empty((scorer.B, beam), dtype=torch.int32, device=scorer.dev)
+    other = scorer.empty_state(state)
+    out = (torch.empty((scorer.B, beam, scorer.C), dtype=torch.float64, device=scorer.dev),
+           torch.empty((scorer.B, beam), dtype=torch.float64, device=scorer.dev))
     for step in range(max_len):
-        psi, psi_eos = scorer.score(state)
+        psi, psi_eos = scorer.score(state, out=out)
         att = att_logp_fn(step, state)
-        new, sel_h, sel_l = scorer.select(state, psi, psi_eos, att, ctc_weight=ctc_weight, eos=eos)
-        new["r"] = scorer.advance(state, sel_h, sel_l, new_flag=new["flag"])
-        state = new
+        new, sel_h, sel_l = scorer.select(state, psi, psi_eos, att, ctc_weight=ctc_weight, eos=eos, out=other)
+        scorer.advance(state, sel_h, sel_l, new_flag=new["flag"], out=new["r"])
+        state, other = new, state
     return state["tokens"], state["score"], state["glen"], state["flag"]

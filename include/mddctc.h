@@ -232,13 +232,18 @@ int mdd_exp_transpose(const float* log_probs, int T, int B, int C, float* probs,
  * absent from the reference as a function -- nearest reference code is BeamSearch.py:52-66,99-125).
  *
  * x      : (T,B,C) fp32 log-probs contiguous; input_lengths int64[B] or NULL.
- * Arithmetic and state are fp64 (log-likelihoods of magnitude |nll|; the beam is chosen by their differences).
- * r_prev : (B,W,T,2) fp64 [r_n, r_b] per hypothesis (mdd_prefix_init fills the empty-prefix state for w = 0..W-1).
+ * p_lin  : (B,T,C) fp64 emission probabilities exp(x), utterance-major, made once per utterance batch by
+ *          mdd_prefix_probs (caller-allocated, T*B*C doubles); score and advance read it instead of x.
+ * Arithmetic and state are fp64 (log-likelihoods of magnitude |nll|; the beam is chosen by their differences).  The
+ * scans over t run in the linear domain relative to each hypothesis' own maximum; state entries more than e^-708
+ * below that maximum are stored as -inf (csrc/prefix_score.cu).
+ * r_prev : (B,W,T,2) fp64 [log r_n, log r_b] per hypothesis (mdd_prefix_init fills the empty-prefix state, w = 0..W-1).
  * last   : int32 (B,W) last label of each hypothesis (-1 = empty), glen int32 (B,W) hypothesis lengths.
  * skip   : optional int32 (B,W): non-zero = hypothesis is finished (1) or dead (2); it is not extended (psi = -inf).
  * psi    : (B,W,C) fp64 out: log p_ctc(g.c, ...); psi[...,blank] = -inf.   psi_eos (B,W) = log p_ctc(g) (optional).
- * mdd_prefix_advance recomputes and stores the state of the chosen (parent hypothesis, label) pairs:
+ * mdd_prefix_advance computes and stores the state of the chosen (parent hypothesis, label) pairs:
  * sel_hyp, sel_label int32 (B,W) -> r_new (B,W,T,2); slots with skip_new != 0 or sel_hyp < 0 are left untouched.
+ * T is limited by shared memory (one hypothesis' linearised state per CTA): T <= 12000, else MDD_E_UNSUPPORTED.
  * mdd_prefix_select is the beam step between the two (nearest reference code: the sort + [:beamWidth] of
  * BeamSearch.py:52-57): per utterance, over all W*C candidates,
  *     value(w,c) = score[w] + ctc_weight * (psi[w,c] - psi_prev[w]) + (1 - ctc_weight) * att[w,c]     (c != blank)
@@ -249,10 +254,11 @@ int mdd_exp_transpose(const float* log_probs, int T, int B, int C, float* probs,
  * ------------------------------------------------------------------------------------------------------------------ */
 int mdd_prefix_init(const float* x, int T, int B, int C, const int64_t* input_lengths, int blank, int W,
                     double* r0, mdd_stream_t stream);
-int mdd_prefix_score(const float* x, int T, int B, int C, const int64_t* input_lengths, int blank, int W,
+int mdd_prefix_probs(const float* x, int T, int B, int C, double* p_lin, mdd_stream_t stream);
+int mdd_prefix_score(const double* p_lin, int T, int B, int C, const int64_t* input_lengths, int blank, int W,
                      const double* r_prev, const int32_t* last, const int32_t* glen, const int32_t* skip, double* psi,
                      double* psi_eos, mdd_stream_t stream);
-int mdd_prefix_advance(const float* x, int T, int B, int C, const int64_t* input_lengths, int blank, int W,
+int mdd_prefix_advance(const double* p_lin, int T, int B, int C, const int64_t* input_lengths, int blank, int W,
                        const double* r_prev, const int32_t* last, const int32_t* glen, const int32_t* sel_hyp,
                        const int32_t* sel_label, const int32_t* skip_new, double* r_new, mdd_stream_t stream);
 int mdd_prefix_select(int B, int W, int C, int blank, int eos, double ctc_weight, int max_len, const double* psi,
