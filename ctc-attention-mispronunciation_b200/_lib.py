@@ -93,7 +93,7 @@ class PostOut(C.Structure):
 
 
 EXPORTS = ["mdd_version", "mdd_error_string", "mdd_launch_count", "mdd_launch_count_reset",
-           "mdd_ctc_loss_workspace_bytes", "mdd_ctc_loss", "mdd_ctc_loss_logits", "mdd_row_lse", "mdd_copy_h2d_2d", "mdd_ctc_scale_grad", "mdd_greedy_decode", "mdd_collapse", "mdd_post_align", "mdd_corpus_counts",
+           "mdd_ctc_loss_workspace_bytes", "mdd_ctc_loss", "mdd_ctc_loss_static", "mdd_ctc_loss_logits", "mdd_row_lse", "mdd_copy_h2d_2d", "mdd_ctc_scale_grad", "mdd_greedy_decode", "mdd_collapse", "mdd_post_align", "mdd_corpus_counts",
            "mdd_edit_align_workspace_bytes", "mdd_edit_align", "mdd_beam_search_workspace_bytes", "mdd_beam_search",
            "mdd_exp_transpose", "mdd_prefix_init", "mdd_prefix_probs", "mdd_prefix_score", "mdd_prefix_advance", "mdd_prefix_select"]
 
@@ -119,6 +119,7 @@ def lib():
     L.mdd_launch_count_reset.restype = None
     L.mdd_ctc_loss_workspace_bytes.argtypes = [i, i, i, i, i, C.POINTER(sz)]
     L.mdd_ctc_loss.argtypes = [vp, i, i, i, i64, i64, vp, i64, vp, vp, i, i, i, vp, f, vp, vp, vp, vp, i, vp, sz, vp]
+    L.mdd_ctc_loss_static.argtypes = [vp, i, i, i, i64, i64, vp, i64, vp, vp, i, i, i, vp, f, vp, vp, vp, vp, i, vp]
     L.mdd_ctc_loss_logits.argtypes = [vp, i, i, i, i64, i64, vp, i64, vp, vp, i, i, i, vp, f, vp, vp, vp, vp, vp, vp, i,
                                       vp, sz, vp]
     L.mdd_row_lse.argtypes = [vp, i, i, i, i64, i64, vp, vp, vp]

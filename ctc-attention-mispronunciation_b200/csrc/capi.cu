@@ -28,6 +28,9 @@ extern "C" const char* mdd_error_string(int code) {
         case MDD_E_WORKSPACE: return "workspace too small";
         case MDD_E_CUDA: return "CUDA runtime error (no device, or launch failure)";
         case MDD_E_UNSUPPORTED: return "shape not supported by this build";
+        case MDD_E_STATIC_LIMIT:
+            return "shape needs more scratch than the library's static array holds (MDD_CTC_STATIC_WS_BYTES); "
+                   "call mdd_ctc_loss with a caller-supplied workspace";
         default: return "unknown error";
     }
 }
@@ -154,6 +157,49 @@ extern "C" int mdd_ctc_loss_logits(const float* logits, int T, int B, int C, int
     return ctc_loss_impl(logits, T, B, C, stride_t, stride_b, targets, tgt_stride, input_lengths, target_lengths,
                          max_target_len, blank, zero_infinity, grad_out, grad_out_scalar, nll, grad_logits, loss_sum,
                          status, row_lse, argmax, algo, workspace, workspace_bytes, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// mdd_ctc_loss_static: mdd_ctc_loss with its scratch in a file-scope device array, for callers that cannot allocate
+// (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// In host code the array's NAME is only a handle for the runtime; its device address comes from
+// cudaGetSymbolAddress, taken once per device with that device current.
+namespace {
+__device__ __align__(256) unsigned char g_ctc_static_ws[MDD_CTC_STATIC_WS_BYTES];
+
+int ctc_static_ws_address(void** out) {
+    static void* addr[64];                                       // per device; every writer stores the same value
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { cudaGetLastError(); return MDD_E_CUDA; }
+    void* p = addr[dev];
+    if (!p) {
+        if (cudaGetSymbolAddress(&p, g_ctc_static_ws) != cudaSuccess || !p) { cudaGetLastError(); return MDD_E_CUDA; }
+        addr[dev] = p;
+    }
+    *out = p;
+    return MDD_OK;
+}
+}  // namespace
+
+extern "C" int mdd_ctc_loss_static(const float* log_probs, int T, int B, int C, int64_t stride_t, int64_t stride_b,
+                                   const int64_t* targets, int64_t tgt_stride, const int64_t* input_lengths,
+                                   const int64_t* target_lengths, int max_target_len, int blank, int zero_infinity,
+                                   const float* grad_out, float grad_out_scalar, float* nll, float* grad,
+                                   float* loss_sum, int32_t* status, int algo, mdd_stream_t stream) {
+    if (T < 0 || B < 0 || C <= 0 || C > MDD_MAX_CLASSES || max_target_len < 0 || blank < 0 || blank >= C || algo < 0 ||
+        algo > 2)
+        return MDD_E_ARG;
+    if (B == 0) return MDD_OK;
+    const CtcWs w = ctc_ws_layout(T, B, C, max_target_len, algo);
+    if (w.total > (size_t)MDD_CTC_STATIC_WS_BYTES) return MDD_E_STATIC_LIMIT;
+    void* ws = nullptr;
+    const int rc = ctc_static_ws_address(&ws);
+    if (rc) return rc;
+    // the array keeps the previous call's contents: target offsets, flags and the flagged list start from zero
+    if (cudaMemsetAsync(ws, 0, w.off_ckpt, (cudaStream_t)stream) != cudaSuccess) { cudaGetLastError(); return MDD_E_CUDA; }
+    return ctc_loss_impl(log_probs, T, B, C, stride_t, stride_b, targets, tgt_stride, input_lengths, target_lengths,
+                         max_target_len, blank, zero_infinity, grad_out, grad_out_scalar, nll, grad, loss_sum, status,
+                         nullptr, nullptr, algo, ws, (size_t)MDD_CTC_STATIC_WS_BYTES, stream);
 }
 
 extern "C" int mdd_copy_h2d_2d(void* dst, size_t dst_pitch, const void* src_host, size_t src_pitch, size_t width_bytes,

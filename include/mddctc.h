@@ -33,7 +33,8 @@ enum {
     MDD_E_ARG = -1,       /* null pointer / negative size / C out of range            */
     MDD_E_WORKSPACE = -2, /* workspace too small                                       */
     MDD_E_CUDA = -3,      /* CUDA runtime error (launch failure, no device)            */
-    MDD_E_UNSUPPORTED = -4
+    MDD_E_UNSUPPORTED = -4,
+    MDD_E_STATIC_LIMIT = -5 /* mdd_ctc_loss_static: the shape needs more than MDD_CTC_STATIC_WS_BYTES of scratch */
 };
 
 enum {                    /* per-utterance status codes                                 */
@@ -107,6 +108,26 @@ int mdd_ctc_loss_logits(const float* logits, int T, int B, int C, int64_t stride
                         const float* grad_out, float grad_out_scalar, float* nll, float* grad_logits, float* loss_sum,
                         int32_t* status, float* row_lse, uint8_t* argmax, int algo, void* workspace,
                         size_t workspace_bytes, mdd_stream_t stream);
+/* mdd_ctc_loss without a workspace argument: the scratch is a static device array inside the library.
+ * This entry point has no counterpart in the reference; it was added for callers
+ * that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  It calls no cudaMalloc / cudaFree and no allocating library routine; arguments, results and kernels are
+ * those of mdd_ctc_loss.
+ *   - Limit: shapes whose mdd_ctc_loss_workspace_bytes(T, B, C, max_target_len, algo) exceeds MDD_CTC_STATIC_WS_BYTES
+ *     (16 MiB: e.g. B = 64 at T = 500, or B = 16 at T = 2000, with algo 0) are rejected with MDD_E_STATIC_LIMIT.
+ *   - Every GPU that loads the library holds the 16 MiB until the process exits.
+ *   - All calls on a device share the one array, which keeps the previous call's contents (the entry point clears the
+ *     part that must start at zero on `stream`): calls that overlap on the GPU -- different streams, or threads --
+ *     race; serialise them or use mdd_ctc_loss with separate workspaces.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that call before
+ *     starting a graph capture. */
+#define MDD_CTC_STATIC_WS_BYTES (16u << 20)
+int mdd_ctc_loss_static(const float* log_probs, int T, int B, int C, int64_t stride_t, int64_t stride_b,
+                        const int64_t* targets, int64_t tgt_stride, const int64_t* input_lengths,
+                        const int64_t* target_lengths, int max_target_len, int blank, int zero_infinity,
+                        const float* grad_out, float grad_out_scalar, float* nll, float* grad, float* loss_sum,
+                        int32_t* status, int algo, mdd_stream_t stream);
+
 /* The pre-pass alone: row_lse (T,B) and optional argmax (T,B) of (T,B,C) logits with strides (stride_t, stride_b, 1). */
 int mdd_row_lse(const float* logits, int T, int B, int C, int64_t stride_t, int64_t stride_b, float* row_lse,
                 uint8_t* argmax, mdd_stream_t stream);
