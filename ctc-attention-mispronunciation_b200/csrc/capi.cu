@@ -52,7 +52,7 @@ CtcWs ctc_ws_layout(int T, int B, int C, int Lmax, int algo) {
     size_t o = 0;
     w.off_offsets = o; o = align_up(o + (size_t)B * 8, 256);
     w.off_flags = o;   o = align_up(o + (size_t)B * 4, 256);
-    w.off_list = o;    o = align_up(o + (size_t)(B + 1) * 4, 256);     // second tier: flagged utterances + their count
+    w.off_list = o;    o = align_up(o + (size_t)(B + 2) * 4, 256);     // second tier: flagged utterances + their count; ticket
     w.off_ckpt = o;
     const int kern = ctc_kernel_choice(C, Lmax, algo);           // 0 fp64 kernel only, 1 pair kernel
     if (algo != 2) o = align_up(o + ctc_exact_ckpt_bytes(T, B, Lmax), 256);
@@ -101,6 +101,7 @@ int ctc_loss_impl(const float* log_probs, int T, int B, int C, int64_t stride_t,
     if (algo == 0) {                                             // the packed kernel's second tier (ctc_pair.cu)
         p.list = reinterpret_cast<int32_t*>(ws + w.off_list);
         p.list_count = p.list + B;
+        if (loss_sum) p.ticket = reinterpret_cast<unsigned*>(p.list + B + 1);
     }
     int rc;
     if (tgt_stride == 0) {
@@ -121,8 +122,10 @@ int ctc_loss_impl(const float* log_probs, int T, int B, int C, int64_t stride_t,
         if (rc) return rc;
         if (algo == 0) {
             p.only_flagged = 1;
+            p.loss_sum = loss_sum;                               // summed by the last CTA of this sweep (ticket zeroed above)
             rc = launch_ctc_exact(p, st);
             if (rc) return rc;
+            if (loss_sum) return MDD_OK;
         }
     } else {
         p.only_flagged = 0;

@@ -338,6 +338,30 @@ __global__ void __launch_bounds__(NT) ctc_exact_kernel(CtcParams p) {
             }
         }
     }
+    // Loss sum in the same launch: the last CTA to get here adds up nll[B] in a fixed order (thread i takes i, i + NT,
+    // ..., then a fixed tree) -- bitwise reproducible, and one launch fewer on the path where nothing was flagged.
+    if (p.ticket && p.loss_sum) {
+        __shared__ int s_last;
+        __shared__ float s_part[NT];
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            s_last = atomicAdd(p.ticket, 1u) == gridDim.x - 1;
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            float s = 0.f;
+            for (int i = tid; i < p.B; i += NT) s += __ldcg(p.nll + i);
+            s_part[tid] = s;
+            __syncthreads();
+            for (int d = NT / 2; d > 0; d >>= 1) {
+                if (tid < d) s_part[tid] += s_part[tid + d];
+                __syncthreads();
+            }
+            if (tid == 0) *p.loss_sum = s_part[0];
+        }
+    }
 }
 
 // exclusive prefix sum of target_lengths (1-D concatenated targets), one block

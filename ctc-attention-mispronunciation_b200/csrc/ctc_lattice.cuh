@@ -177,5 +177,49 @@ __device__ __forceinline__ void renorm_alpha(float2 (&a)[NSL], int (&ea)[2], flo
     sca = make_float2(lane == 0 ? 0.f : pow2i(nb0 - new0), lane == 0 ? 0.f : pow2i(nb1 - new1));
 }
 
+// The mirror image for a beta sweep that carries its own exponents (ctc_dual.cu): mass enters a lane from its RIGHT
+// neighbour, so a lane is kept within 2^GAP of lane l+1 and the max-scan runs downwards.  scb = 2^(e[l+1] - e[l])
+// (0 on lane 31) is the factor beta_step applies to what it receives.  Same guards as renorm_alpha.
+template <int NSL>
+__device__ __forceinline__ void renorm_beta(float2 (&b)[NSL], int (&eb)[2], float2& scb, int lane, bool (&ok)[2],
+                                            int decay_max = 1 << 20) {
+    constexpr int GAP = PGeo<NSL>::GAP;
+    float m0 = b[0].x, m1 = b[0].y;
+#pragma unroll
+    for (int j = 1; j + 1 < NSL; j += 2) {
+        m0 = fmax3(m0, b[j].x, b[j + 1].x);
+        m1 = fmax3(m1, b[j].y, b[j + 1].y);
+    }
+    m0 = fmaxf(m0, b[NSL - 1].x);
+    m1 = fmaxf(m1, b[NSL - 1].y);
+    const int k0 = ((__float_as_int(m0) >> 23) & 0xff) - 127, k1 = ((__float_as_int(m1) >> 23) & 0xff) - 127;
+    const bool some0 = m0 >= 1.17549435e-38f && m0 < 3.0e38f;
+    const bool some1 = m1 >= 1.17549435e-38f && m1 < 3.0e38f;
+    const int own0 = some0 ? eb[0] + k0 - SHIFT : E_EMPTY, own1 = some1 ? eb[1] + k1 - SHIFT : E_EMPTY;
+    int t0 = own0 - GAP * lane, t1 = own1 - GAP * lane;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {                            // lanes >= 32 - d get their own value back
+        const int s0 = __shfl_down_sync(FULL, t0, d), s1 = __shfl_down_sync(FULL, t1, d);
+        t0 = max(t0, s0);
+        t1 = max(t1, s1);
+    }
+    const int new0 = t0 + GAP * lane, new1 = t1 + GAP * lane;
+    const int nb0 = __shfl_down_sync(FULL, new0, 1), nb1 = __shfl_down_sync(FULL, new1, 1);
+    const int top0 = __reduce_max_sync(FULL, own0), top1 = __reduce_max_sync(FULL, own1);
+    const bool fast0 = some0 && own0 >= top0 - 64 && k0 - SHIFT < -decay_max;
+    const bool fast1 = some1 && own1 >= top1 - 64 && k1 - SHIFT < -decay_max;
+    const bool bad0 = (m0 != m0) || m0 >= 3.0e38f || fast0;
+    const bool bad1 = (m1 != m1) || m1 >= 3.0e38f || fast1;
+    const unsigned bits = __reduce_or_sync(FULL, (some0 ? 1u : 0u) | (bad0 ? 2u : 0u) | (some1 ? 4u : 0u) | (bad1 ? 8u : 0u));
+    ok[0] = (bits & 3u) == 1u;
+    ok[1] = (bits & 12u) == 4u;
+    const float2 f2 = make_float2(pow2i(eb[0] - new0), pow2i(eb[1] - new1));
+    eb[0] = new0;
+    eb[1] = new1;
+#pragma unroll
+    for (int j = 0; j < NSL; ++j) b[j] = __fmul2_rn(b[j], f2);
+    scb = make_float2(lane == 31 ? 0.f : pow2i(nb0 - new0), lane == 31 ? 0.f : pow2i(nb1 - new1));
+}
+
 }  // namespace lattice
 }  // namespace mdd

@@ -91,9 +91,14 @@ __host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf, int p
 // PHASE 0: both sweeps in one kernel.  PHASE 1: the forward sweep alone (loss, checkpoints, a record of P per
 // utterance) -- it needs a third of the registers, so two to three times as many warps share an SM; PHASE 2: the
 // backward sweep alone, from the checkpoints and the record.
-template <int NSL, bool REGBUF, bool LOGITS, int CH, bool LIST, int PHASE = 0>
+// SEG (with PHASE 2): the backward sweep of ONE SEGMENT of the pair's chunks, [seg * nch / nseg, (seg + 1) * nch / nseg):
+// beta enters from the checkpoint the concurrent beta sweep of ctc_dual.cu left at the segment's upper end (its own
+// exponents; from there on they are tied to alpha's as everywhere else), the emission-row layout comes from the
+// workspace.  Segments of a pair are independent of each other, so few utterances still fill the machine.
+template <int NSL, bool REGBUF, bool LOGITS, int CH, bool LIST, int PHASE = 0, bool SEG = false>
 __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restrict__ ckpt_ws, int n_ckpt, int pair,
-                                              int slot, int n_utt) {
+                                              int slot, int n_utt, int seg = 0) {
+    static_assert(!SEG || (PHASE == 2 && !LIST), "segments: backward kernel of the first pass only");
     using G = PGeo<NSL>;
     constexpr int NL = G::NL, ARS = G::ARS, CKW = G::CKW;
     static_assert(CH >= 1 && CH <= KF && (CH & (CH - 1)) == 0, "chunk length: a power of two up to the staged rows");
@@ -163,6 +168,9 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     // none of its groups.
     int* gm = scratch + 1280;                                    // [2][72] gather-group mask per item
     int* cpos = scratch + 1280 + 144;                            // [2][72] position per item
+    if constexpr (SEG) {
+        for (int i = lane; i < 144; i += 32) cpos[i] = p.cpos_ws[(size_t)pair * 144 + i];
+    } else {
     for (int i = lane; i < 144; i += 32) gm[i] = 0;
     __syncwarp();
 #pragma unroll
@@ -210,6 +218,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
 #pragma unroll
         for (int k = 0; k < 3; ++k)
             if (valid[k]) cpos[h * 72 + lane + 32 * k] = posk[k];
+    }
     }
     __syncwarp();
     // Row ownership follows the layout: lane l commits (and later differentiates) the class placed in bank l of each
@@ -312,6 +321,10 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         t0 = Tmin + nS8 * CH + (j - cS);
         return false;
     };
+    // the chunks this warp sweeps backwards: all of them, or its segment
+    const int jlo = SEG ? (int)((long long)seg * nch / p.nseg) : 0;
+    const int jhi = SEG ? (int)((long long)(seg + 1) * nch / p.nseg) : nch;
+    if (SEG && jlo >= jhi) return;
     // rows are always read from a live utterance's memory; an idle half re-reads its partner's rows
     const int bsrc0 = act[0] ? bidx[0] : bidx[1], bsrc1 = act[1] ? bidx[1] : bidx[0];
     const float* lpb0 = p.lp + (size_t)bsrc0 * p.stride_b;
@@ -339,7 +352,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     const unsigned raw_s = (unsigned)__cvta_generic_to_shared(raw);
     const unsigned tstride_b = (unsigned)(p.stride_t * 4);       // row pitch in bytes (< 4 GB, checked by the launcher)
     auto issue_rows = [&](int j) {                       // rows of chunk j -> slot j % NSLOT (its own cp.async group)
-        if (j >= 0 && j < nch) {
+        if (j >= jlo && j < nch) {
             int t0;
             const bool full = chunk_geom(j, t0);
             const int so = (j % NSLOT) * (KF * RAWW);
@@ -456,7 +469,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         issue_rows(0);
         if constexpr (NSLOT == 3) issue_rows(1);
     }
-    if (want_grad && PHASE != 1) {                      // rows t >= T_max of the gradient are zero (torch semantics)
+    if (want_grad && PHASE != 1 && jhi == nch) {        // rows t >= T_max of the gradient are zero (torch semantics)
         for (int t = Tmax; t < T; ++t)
             for (int i = lane; i < C; i += 32) {
                 if (act[0]) __stcs(gr0 + (size_t)t * gstride + i, 0.f);
@@ -574,7 +587,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     // and are picked up with LDS.
     const unsigned ckst_s = (unsigned)__cvta_generic_to_shared(ckst);
     auto ckpt_issue = [&](int j) {
-        if (j >= 0) {
+        if (j >= jlo) {
             const float* c = ck + (size_t)j * CKW;
 #pragma unroll
             for (int q = 0; q < NSL / 2; ++q)
@@ -761,10 +774,19 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
 
     // in flight when chunk j starts, oldest first: rows(j), checkpoint(j), rows(j - 1); in the single kernel the last
     // chunk's rows are still staged from the forward sweep
-    if constexpr (PHASE == 2) issue_rows(nch - 1);
-    ckpt_issue(nch - 1);
-    issue_rows(nch - 2);
-    for (int j = nch - 1; j >= 0; --j) {
+    if constexpr (SEG) {
+        if (jhi < nch) {                                // beta entering chunk jhi - 1 from above, with the beta sweep's own exponents
+            const float* c = p.ckb + ((size_t)slot * n_ckpt + (jhi - 1)) * CKW;
+#pragma unroll
+            for (int q = 0; q < NSL; ++q) bt[q] = reinterpret_cast<const float2*>(c)[q * 32 + lane];
+            const int2 e = reinterpret_cast<const int2*>(c + 64 * NSL)[lane];
+            eb[0] = e.x; eb[1] = e.y;
+        }
+    }
+    if constexpr (PHASE == 2) issue_rows(jhi - 1);
+    ckpt_issue(jhi - 1);
+    issue_rows(jhi - 2);
+    for (int j = jhi - 1; j >= jlo; --j) {
         int t0;
         if (chunk_geom(j, t0)) bwd_chunk(IC<CH>{}, j, t0);
         else bwd_chunk(IC<1>{}, j, t0);
@@ -784,7 +806,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         // The backward sweep's own total likelihood, beta_0(0) + beta_0(1), against the forward P.  Mass dropped by
         // either sweep (alpha content squashed in a renormalisation, beta content below its tied exponent) is missing
         // from exactly one of the two, so their ratio bounds what the occupancies can be off by.
-        {
+        if (!SEG || jlo == 0) {
             const float r0 = (bt[0].x + bt[1].x) * pow2i(-ea[0]) * zi[0];
             const float r1 = (bt[0].y + bt[1].y) * pow2i(-ea[1]) * zi[1];
             const int disagree = (!(fabsf(r0 - 1.f) <= p.pbeta_tol) ? 1 : 0) | (!(fabsf(r1 - 1.f) <= p.pbeta_tol) ? 2 : 0);
@@ -796,16 +818,22 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
             if ((d0 & 2) && act[1] && !flag[1]) flag[1] = 7;
         }
 #pragma unroll
-        for (int h = 0; h < 2; ++h)
-            if (act[h] && lane == 0) p.flags[bidx[h]] = flag[h];   // 0 = done here; else redone by the next tier
+        for (int h = 0; h < 2; ++h)                          // 0 = done here; else redone by the next tier.  Segments share the
+            if (act[h] && lane == 0 && (!SEG || flag[h])) p.flags[bidx[h]] = flag[h];   // word: each only ever raises it
     }
 }
 
-template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST, int PHASE = 0>
+template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST, int PHASE = 0, bool SEG = false>
 __global__ void __maxnreg__(MAXR)
 ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if constexpr (!LIST) {
+    if constexpr (!LIST && !SEG && PHASE != 2) {                 // first kernel of the call (see ctc_exact.cu)
+        if (p.ticket && blockIdx.x == 0 && threadIdx.x == 0) *p.ticket = 0u;
+    }
+    if constexpr (SEG) {
+        const int pr = w / p.nseg;                               // segments of a pair sit in neighbouring CTAs
+        if (pr < ((p.B + 1) >> 1)) ctc_pair_body<NSL, REGBUF, LOGITS, CH, false, PHASE, true>(p, ckpt_ws, n_ckpt, pr, pr, p.B, w - pr * p.nseg);
+    } else if constexpr (!LIST) {
         if (w < ((p.B + 1) >> 1)) ctc_pair_body<NSL, REGBUF, LOGITS, CH, false, PHASE>(p, ckpt_ws, n_ckpt, w, w, p.B);
     } else {
         // second tier: this warp owns checkpoint block w and walks the pairs w, w + #warps, ... of the flagged list
@@ -818,6 +846,10 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         }
     }
 }
+
+constexpr int kDualMaxPairs = 4 * kNumSM;                        // the concurrent-sweep path serves up to this many pairs
+// floats from the start of the pair workspace to the beta checkpoints: alpha checkpoints, one record per utterance
+size_t dual_beta_offset(size_t ck_floats, int B) { return (ck_floats + ((size_t)B + 2) * 4 + 63) & ~(size_t)63; }
 
 int pick_nsl(int Lmax) {
     if (Lmax <= PGeo<2>::LCAP) return 2;
@@ -860,7 +892,7 @@ __global__ void __launch_bounds__(1024) compact_flagged_kernel(const int32_t* __
     if (tid == 0) *count = base;
 }
 
-template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST, int PHASE = 0>
+template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST, int PHASE = 0, bool SEG = false>
 int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st, int npairs) {
     const PairSmem lay = pair_smem_layout(NSL, REGBUF, PHASE);
     size_t smem = (size_t)lay.total_floats * 4;                  // one warp (= one pair) per CTA
@@ -882,13 +914,13 @@ int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st, int npairs) {
         const size_t want = ((233472 / (size_t)wps) - 1024 - 64) & ~(size_t)15;
         if (want > smem && want <= 227 * 1024) smem = want;
     }
-    if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST, PHASE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if (cudaFuncSetAttribute(ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST, PHASE, SEG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)smem) != cudaSuccess) {                // per device: set on every call (cheap)
         cudaGetLastError();
         return MDD_E_CUDA;
     }
     const int n_ckpt = p.T / CH + 2 * CH;
-    ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST, PHASE><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
+    ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST, PHASE, SEG><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
     MDD_CHECK_LAUNCH();
     return MDD_OK;
 }
@@ -903,8 +935,23 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
     const bool team_ok = ctc_team_supported(p.C, p.Lmax);
     int rc;
     static int split = env_int("MDD_CTC_SPLIT", 1);
-    p.rec = reinterpret_cast<float4*>(ws + (size_t)npairs * (p.T / KF + 2 * KF) * PGeo<NSL>::CKW);
-    if (team_ok && npairs <= team_max) rc = launch_ctc_team(p, ws, st, false, npairs);
+    const size_t ck_floats = (size_t)npairs * (p.T / KF + 2 * KF) * PGeo<NSL>::CKW;
+    p.rec = reinterpret_cast<float4*>(ws + ck_floats);
+    // Fewer still (and a gradient wanted): alpha and beta swept concurrently by ctc_dual.cu, then the backward kernel on
+    // independent segments of every pair -- the dependent chain is T lattice steps instead of 3 T.
+    static int dual_max = std::min(env_int("MDD_CTC_DUAL_MAX_PAIRS", 2 * kNumSM), kDualMaxPairs);   // beyond: no faster (measured)
+    static int nseg_env = env_int("MDD_CTC_DUAL_NSEG", 0);
+    if (team_ok && p.grad && npairs <= dual_max) {
+        float* ckb = ws + dual_beta_offset(ck_floats, p.B);
+        p.ckb = ckb;
+        p.cpos_ws = reinterpret_cast<int*>(ckb + ck_floats);
+        rc = launch_ctc_dual(p, ws, ckb, st, npairs);
+        if (!rc) {
+            const int want = nseg_env > 0 ? nseg_env : (7 * sm_count()) / npairs;     // one wave of 7 warps per SM
+            p.nseg = std::max(1, std::min(want, std::max(1, p.T / KF)));
+            rc = launch_cfg1<NSL, REGBUF, MAXR, LOGITS, KF, false, 2, true>(p, ws, st, npairs * p.nseg);
+        }
+    } else if (team_ok && npairs <= team_max) rc = launch_ctc_team(p, ws, st, false, npairs);
     else if (split || !p.grad) {
         // forward sweep at high occupancy (a third of the registers), then the backward sweep from its checkpoints
         rc = launch_cfg1<NSL, REGBUF, 128, LOGITS, KF, false, 1>(p, ws, st, npairs);
@@ -927,6 +974,7 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
     if (p.list_team_max > 0) {
         rc = launch_ctc_team(p, ws, st, true, std::min(cap, 2 * sm_count()));
         if (rc) return rc;
+        if (p.B <= p.list_team_max) return MDD_OK;               // the whole batch fits the team kernel's share: nothing can be left
     }
     return launch_cfg1<NSL, REGBUF, MAXR, LOGITS, CH2, true>(p, ws, st, cap);
 }
@@ -964,7 +1012,10 @@ size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
     const int nsl = pick_nsl(Lmax);
     if (!nsl) return 0;
     const size_t n_ckpt = (size_t)T / KF + 2 * KF;
-    return (size_t)((B + 1) / 2) * n_ckpt * 32 * (2 * nsl + 2) * 4 + ((size_t)B + 2) * 16;   // + one record per utterance
+    const size_t npairs = (size_t)((B + 1) / 2), ck_floats = npairs * n_ckpt * 32 * (2 * nsl + 2);
+    if ((int)npairs <= kDualMaxPairs)                            // + beta checkpoints and the emission-row layouts (ctc_dual.cu)
+        return (dual_beta_offset(ck_floats, B) + ck_floats + npairs * 144 + 64) * 4;
+    return ck_floats * 4 + ((size_t)B + 2) * 16;                 // + one record per utterance
 }
 #endif
 

@@ -39,6 +39,15 @@ struct CtcParams {
     int list_team_max;        // second tier: up to this many flagged utterances go to the team kernel, more to the pair kernel
     int decay_max;            // largest per-chunk decay (bits) of the lanes holding the bulk of alpha
     float4* rec;              // [B] forward kernel -> backward kernel: 1 / mantissa(P), exponent, flag
+    // few utterances (ctc_dual.cu + the SEG instantiation of ctc_pair.cu): beta checkpoints, the emission-row layout of
+    // every pair ([npairs][2][72] positions), segments per pair of the backward kernel
+    float* ckb;
+    int* cpos_ws;
+    int nseg;
+    // loss sum folded into the fp64 kernel's launch: the first kernel of a call zeroes the ticket, the last CTA of the
+    // fp64 sweep to finish adds up nll[B] in a fixed order (null: the caller launches sum_nll_kernel instead)
+    unsigned* ticket;
+    float* loss_sum;
 };
 
 // fp64 linear-domain kernel, one CTA per utterance (ctc_exact.cu): robust path and per-utterance fallback
@@ -55,6 +64,10 @@ int launch_ctc_pair(CtcParams p, void* ws, cudaStream_t st);
 // one CTA per pair, lattice warp + helper warps (ctc_team.cu): few utterances per SM, and the second tier
 bool ctc_team_supported(int C, int Lmax);
 int launch_ctc_team(const CtcParams& p, void* ws, cudaStream_t st, bool list, int nblocks);
+
+// few utterances: alpha and beta swept concurrently, checkpoints of both (ctc_dual.cu); the gradient is then the backward
+// kernel of ctc_pair.cu on many segments of every pair at once
+int launch_ctc_dual(const CtcParams& p, float* cka, float* ckb, cudaStream_t st, int npairs);
 
 // per-frame log-sum-exp (+ argmax) of logits (row_lse.cu): the pre-pass of mdd_ctc_loss_logits
 int launch_row_lse(const float* x, int T, int B, int C, int64_t stride_t, int64_t stride_b, float* lse, uint8_t* amax,

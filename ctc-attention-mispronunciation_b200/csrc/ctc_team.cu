@@ -733,6 +733,7 @@ template <int NSL, int NH, bool LOGITS, int CH, bool LIST>
 __global__ void __launch_bounds__(32 * (1 + NH), 2) ctc_team_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     extern __shared__ __align__(16) float team_smem[];
     if constexpr (!LIST) {
+        if (p.ticket && blockIdx.x == 0 && threadIdx.x == 0) *p.ticket = 0u;   // first kernel of the call (see ctc_exact.cu)
         ctc_team_body<NSL, NH, LOGITS, CH, false>(p, ckpt_ws, n_ckpt, blockIdx.x, blockIdx.x, p.B, team_smem, true);
     } else {
         // the flagged utterances: this CTA owns checkpoint block blockIdx.x and walks the pairs blockIdx.x, + grid, ...

@@ -134,7 +134,9 @@ def _aligned_logits(T, B, C, L, il, tl, tg, boost, noise, g):
 ENVELOPE = [  # name, boost (None = unstructured randn * scale), noise / scale, the first pass keeps everything, the
     # second tier (2-frame chunks over the flagged list) leaves nothing for the fp64 kernel
     ("randn*2", None, 2.0, True, True), ("randn*3", None, 3.0, False, True), ("randn*5", None, 5.0, False, False),
-    ("aligned+6", 6, 0.1, True, True), ("aligned+10", 10, 0.1, True, True), ("aligned+10 clean", 10, 0.0, True, True),
+    # (aligned+10: at this batch size the beta sweep of ctc_dual.cu carries its own exponents and its decay guard hands
+    # one utterance of 256 to the second tier; the one-warp-per-pair kernel of larger batches keeps all of them)
+    ("aligned+6", 6, 0.1, True, True), ("aligned+10", 10, 0.1, False, True), ("aligned+10 clean", 10, 0.0, True, True),
     ("aligned+16", 16, 0.1, False, True), ("aligned+25", 25, 0.1, False, False),
     ("aligned+16 noise .3", 16, 0.3, False, True),
 ]
