@@ -19,8 +19,8 @@
 //     exactly as the sequential sweep does), which makes it a throughput kernel whatever the batch size.
 // The two sweeps check each other: beta_0(0) + beta_0(1) from the beta sweep must agree with P from the alpha sweep
 // (flag 7), mass dropped by either renormalisation is missing from exactly one of the two.
-// The bank colouring of the emission row is computed here (one utterance per lattice warp) and handed to the second
-// half through the workspace.
+// The layout of the emission row (bank-coloured for long sweeps, one utterance per lattice warp; plain for short ones)
+// is decided here and handed to the second half through the workspace.
 #include <algorithm>
 #include <cstdlib>
 
@@ -36,6 +36,7 @@ using namespace lattice;
 constexpr int DRAWW = 132;                 // floats per staged pair row: 2*C log-probs (C <= 63) + 2 row-LSE + pad
 constexpr int DNSLOT = 3;                  // raw staging slots per side
 constexpr int DNE = 3;                     // emission buffers per side
+constexpr int kColourMinWork = 1200;       // frames x label states per lane from which the bank colouring pays
 
 template <int NSL, int NH>
 struct DualLayout {
@@ -128,6 +129,11 @@ __global__ void __launch_bounds__(64 * (1 + NH), 2) ctc_dual_kernel(CtcParams p,
         }
         if (lane == 0) { meta[h] = act; meta[2 + h] = Tb; meta[4 + h] = L; }
         __syncwarp();
+        // Short sweeps use the plain emission row, class c at position c, here and in the second half: both are
+        // latency-bound then, a two-way bank conflict in a gather costs a couple of cycles, the colouring ~12000.
+        if (T * NL < kColourMinWork) {
+            for (int i = lane; i < 72; i += 32) cpos[h * 72 + i] = i;
+        } else {
         // bank colouring of this utterance's emission row (see ctc_pair.cu): items = classes 0..C-1 and the zero item C
         for (int i = lane; i < 72; i += 32) gm[h * 72 + i] = 0;
         __syncwarp();
@@ -173,6 +179,8 @@ __global__ void __launch_bounds__(64 * (1 + NH), 2) ctc_dual_kernel(CtcParams p,
             for (int k = 0; k < 3; ++k)
                 if (valid[k]) cpos[h * 72 + lane + 32 * k] = posk[k];
         }
+        }
+        __syncwarp();
         for (int i = lane; i < 64; i += 32) ipos[h * 64 + i] = -1;
         __syncwarp();
         for (int c = lane; c <= C; c += 32) ipos[h * 64 + cpos[h * 72 + c]] = c;
