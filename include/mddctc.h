@@ -72,7 +72,9 @@ void mdd_launch_count_reset(void);
  * grad      : (T,B,C) contiguous fp32 out, or NULL for loss only.  Rows t >= input_lengths[b] are written as 0.
  * loss_sum  : optional fp32 scalar out = sum_b nll[b] (deterministic fixed-order tree), e.g. an NCCL send buffer.
  * status    : optional int32[B].
- * algo      : 0 = auto: packed two-utterances-per-warp fp32 linear-domain kernel at 8 frames per chunk; the utterances
+ * algo      : 0 = auto: packed two-utterances-per-warp fp32 linear-domain kernel at 8 frames per chunk (for up to
+ *                 296 pairs: alpha and beta swept concurrently, one CTA per pair, then the gradient on independent
+ *                 segments of every pair -- same arithmetic, a third of the dependent chain); the utterances
  *                 it flags (dynamic range, malformed rows) again at 2 frames per chunk; what is still flagged by the
  *                 fp64 linear-domain kernel (one CTA per utterance, exact to the rounding of the fp32 outputs),
  *             1 = fp64 kernel only, 2 = first packed pass only (no second tier, no fallback; for profiling).
