@@ -1,9 +1,16 @@
 // capi.cu -- C ABI entry points for the CTC loss (include/mddctc.h) + library bookkeeping.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "ctc_params.cuh"
 
 namespace mdd {
 int64_t g_launch_count = 0;
+
+bool pdl_enabled() {
+    static int on = [] { const char* e = getenv("MDD_PDL"); return e ? atoi(e) : 1; }();
+    return on != 0;
+}
 
 int sm_count() {
     static int cached[64];                                       // per device: one process may drive several GPUs

@@ -36,7 +36,6 @@ using namespace lattice;
 constexpr int DRAWW = 132;                 // floats per staged pair row: 2*C log-probs (C <= 63) + 2 row-LSE + pad
 constexpr int DNSLOT = 3;                  // raw staging slots per side
 constexpr int DNE = 3;                     // emission buffers per side
-constexpr int kColourMinWork = 1200;       // frames x label states per lane from which the bank colouring pays
 
 template <int NSL, int NH>
 struct DualLayout {
@@ -93,6 +92,9 @@ __global__ void __launch_bounds__(64 * (1 + NH), 2) ctc_dual_kernel(CtcParams p,
     const long long dt_start = clock64();
 #endif
 
+    // The whole grid is one wave (at most two CTAs per SM): the second half may be scheduled behind it at once and do its
+    // set-up while the sweeps run (it waits for them with pdl_wait before it touches what they produce).
+    pdl_launch_dependents();
     if (threadIdx.x == 0) {
         if (p.ticket && blockIdx.x == 0) *p.ticket = 0u;         // first kernel of the call (see ctc_exact.cu)
         uint64_t* b0 = reinterpret_cast<uint64_t*>(dual_smem + LY::BAR_OFF);

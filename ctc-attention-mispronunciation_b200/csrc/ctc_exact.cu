@@ -79,6 +79,7 @@ __global__ void __launch_bounds__(NT) ctc_exact_kernel(CtcParams p) {
         return e;
     };
 
+    if (p.only_flagged) pdl_wait();        // launched behind the packed tiers of the same call
     for (int b = blockIdx.x; b < p.B; b += gridDim.x) {
         if (p.only_flagged && p.flags[b] == 0) continue;
         __syncthreads();                   // the previous utterance of this CTA is done with shared memory
@@ -423,7 +424,14 @@ int launch_ctc_exact(CtcParams p, cudaStream_t st) {
     // persistent CTAs: a fallback sweep with nothing flagged reads B flags and leaves
     const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (220 * 1024) / (smem + 1024)));
     const int grid = std::min(p.B, sm_count() * per_sm);
-    ctc_exact_kernel<<<grid, NT, smem, st>>>(p);
+    if (p.only_flagged) {
+        if (launch_dependent(ctc_exact_kernel, dim3(grid), dim3(NT), smem, st, p) != cudaSuccess) {
+            cudaGetLastError();
+            return MDD_E_CUDA;
+        }
+    } else {
+        ctc_exact_kernel<<<grid, NT, smem, st>>>(p);
+    }
     MDD_CHECK_LAUNCH();
     return MDD_OK;
 }

@@ -10,6 +10,7 @@ namespace lattice {
 
 constexpr int KF = 8;                    // frames per chunk = renormalisation period = checkpoint period
 constexpr int E_EMPTY = -(1 << 20);      // exponent of a lane whose states are all zero
+constexpr int kColourMinWork = 1200;     // frames x label states per lane from which the bank colouring pays (ctc_dual.cu)
 #ifndef MDD_SHIFT
 #define MDD_SHIFT 30
 #endif

@@ -169,7 +169,12 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     int* gm = scratch + 1280;                                    // [2][72] gather-group mask per item
     int* cpos = scratch + 1280 + 144;                            // [2][72] position per item
     if constexpr (SEG) {
-        for (int i = lane; i < 144; i += 32) cpos[i] = p.cpos_ws[(size_t)pair * 144 + i];
+        if (p.T * NL < kColourMinWork) {                         // short sweeps: the plain row, nothing to wait for yet
+            for (int i = lane; i < 144; i += 32) cpos[i] = i % 72;
+        } else {
+            pdl_wait();                                          // the layout comes from the sweep kernel
+            for (int i = lane; i < 144; i += 32) cpos[i] = p.cpos_ws[(size_t)pair * 144 + i];
+        }
     } else {
     for (int i = lane; i < 144; i += 32) gm[i] = 0;
     __syncwarp();
@@ -553,6 +558,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         return;
     }
     if constexpr (PHASE == 2) {
+        pdl_wait();                                     // set-up done; from here on the forward kernel's results are read
 #pragma unroll
         for (int h = 0; h < 2; ++h)
             if (act[h]) {
@@ -833,9 +839,13 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     if constexpr (SEG) {
         const int pr = w / p.nseg;                               // segments of a pair sit in neighbouring CTAs
         if (pr < ((p.B + 1) >> 1)) ctc_pair_body<NSL, REGBUF, LOGITS, CH, false, PHASE, true>(p, ckpt_ws, n_ckpt, pr, pr, p.B, w - pr * p.nseg);
+        pdl_launch_dependents();                                 // (at the end: the tier kernels must not take this grid's SMs)
     } else if constexpr (!LIST) {
         if (w < ((p.B + 1) >> 1)) ctc_pair_body<NSL, REGBUF, LOGITS, CH, false, PHASE>(p, ckpt_ws, n_ckpt, w, w, p.B);
+        pdl_launch_dependents();
     } else {
+        pdl_launch_dependents();
+        pdl_wait();
         // second tier: this warp owns checkpoint block w and walks the pairs w, w + #warps, ... of the flagged list
         const int n_utt = *p.list_count, stride = gridDim.x * (blockDim.x >> 5);
         if (n_utt <= p.list_team_max) return;                    // few flagged utterances: the team kernel has taken them
@@ -870,6 +880,8 @@ __global__ void __launch_bounds__(1024) compact_flagged_kernel(const int32_t* __
     __shared__ int wsum[32];
     __shared__ int base;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_launch_dependents();
+    pdl_wait();
     if (tid == 0) base = 0;
     __syncthreads();
     for (int b0 = 0; b0 < B; b0 += 1024) {
@@ -920,7 +932,15 @@ int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st, int npairs) {
         return MDD_E_CUDA;
     }
     const int n_ckpt = p.T / CH + 2 * CH;
-    ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST, PHASE, SEG><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
+    if constexpr (PHASE == 2 || LIST) {                          // behind another kernel of this call: dependent launch
+        if (launch_dependent(ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST, PHASE, SEG>, dim3(npairs), dim3(32), smem, st, p, ws,
+                             n_ckpt) != cudaSuccess) {
+            cudaGetLastError();
+            return MDD_E_CUDA;
+        }
+    } else {
+        ctc_pair_kernel<NSL, REGBUF, MAXR, LOGITS, CH, LIST, PHASE, SEG><<<npairs, 32, smem, st>>>(p, ws, n_ckpt);
+    }
     MDD_CHECK_LAUNCH();
     return MDD_OK;
 }
@@ -963,7 +983,10 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
     const size_t per_pair = (size_t)(p.T / CH2 + 2 * CH2) * PGeo<NSL>::CKW;
     const int cap = (int)std::min<size_t>(ws_floats / per_pair, (size_t)npairs);
     if (cap <= 0) return MDD_OK;
-    compact_flagged_kernel<<<1, 1024, 0, st>>>(p.flags, p.B, p.list, p.list_count);
+    if (launch_dependent(compact_flagged_kernel, dim3(1), dim3(1024), 0, st, (const int32_t*)p.flags, p.B, p.list, p.list_count) != cudaSuccess) {
+        cudaGetLastError();
+        return MDD_E_CUDA;
+    }
     MDD_CHECK_LAUNCH();
     p.list_cap_pairs = cap;
     // Few flagged utterances: one CTA per pair with helper warps (each pair alone on its SM would crawl in the pair

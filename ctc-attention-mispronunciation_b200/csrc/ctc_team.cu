@@ -737,6 +737,8 @@ __global__ void __launch_bounds__(32 * (1 + NH), 2) ctc_team_kernel(CtcParams p,
         ctc_team_body<NSL, NH, LOGITS, CH, false>(p, ckpt_ws, n_ckpt, blockIdx.x, blockIdx.x, p.B, team_smem, true);
     } else {
         // the flagged utterances: this CTA owns checkpoint block blockIdx.x and walks the pairs blockIdx.x, + grid, ...
+        pdl_launch_dependents();
+        pdl_wait();
         const int n_utt = *p.list_count;
         if (n_utt > p.list_team_max) return;                     // many flagged utterances: the pair kernel's second tier takes them
         for (int pr = blockIdx.x; 2 * pr < n_utt; pr += gridDim.x)
@@ -754,7 +756,15 @@ int launch_team1(const CtcParams& p, float* ws, cudaStream_t st, int nblocks) {
         return MDD_E_CUDA;
     }
     const int n_ckpt = p.T / CH + 2 * CH;
-    ctc_team_kernel<NSL, NH, LOGITS, CH, LIST><<<nblocks, 32 * (1 + NH), smem, st>>>(p, ws, n_ckpt);
+    if constexpr (LIST) {
+        if (launch_dependent(ctc_team_kernel<NSL, NH, LOGITS, CH, LIST>, dim3(nblocks), dim3(32 * (1 + NH)), smem, st, p, ws, n_ckpt) !=
+            cudaSuccess) {
+            cudaGetLastError();
+            return MDD_E_CUDA;
+        }
+    } else {
+        ctc_team_kernel<NSL, NH, LOGITS, CH, LIST><<<nblocks, 32 * (1 + NH), smem, st>>>(p, ws, n_ckpt);
+    }
     MDD_CHECK_LAUNCH();
     return MDD_OK;
 }
