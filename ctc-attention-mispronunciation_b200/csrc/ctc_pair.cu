@@ -168,7 +168,10 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     // none of its groups.
     int* gm = scratch + 1280;                                    // [2][72] gather-group mask per item
     int* cpos = scratch + 1280 + 144;                            // [2][72] position per item
-    if constexpr (SEG) {
+    if constexpr (PHASE == 2 && !LIST && !SEG) {                 // the forward kernel has coloured the row of this pair
+        pdl_wait();
+        for (int i = lane; i < 144; i += 32) cpos[i] = p.cpos_ws[(size_t)pair * 144 + i];
+    } else if constexpr (SEG) {
         if (p.T * NL < kColourMinWork) {                         // short sweeps: the plain row, nothing to wait for yet
             for (int i = lane; i < 144; i += 32) cpos[i] = i % 72;
         } else {
@@ -223,6 +226,11 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
 #pragma unroll
         for (int k = 0; k < 3; ++k)
             if (valid[k]) cpos[h * 72 + lane + 32 * k] = posk[k];
+    }
+    if constexpr (PHASE == 1 && !LIST) {                         // ... and hands the layout to the backward kernel
+        __syncwarp();
+        if (want_grad && p.cpos_ws)
+            for (int i = lane; i < 144; i += 32) p.cpos_ws[(size_t)pair * 144 + i] = cpos[i];
     }
     }
     __syncwarp();
@@ -974,6 +982,7 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
     } else if (team_ok && npairs <= team_max) rc = launch_ctc_team(p, ws, st, false, npairs);
     else if (split || !p.grad) {
         // forward sweep at high occupancy (a third of the registers), then the backward sweep from its checkpoints
+        p.cpos_ws = reinterpret_cast<int*>(ws + dual_beta_offset(ck_floats, p.B));
         rc = launch_cfg1<NSL, REGBUF, 128, LOGITS, KF, false, 1>(p, ws, st, npairs);
         if (!rc && p.grad) rc = launch_cfg1<NSL, REGBUF, MAXR, LOGITS, KF, false, 2>(p, ws, st, npairs);
     } else rc = launch_cfg1<NSL, REGBUF, MAXR, LOGITS, KF, false>(p, ws, st, npairs);
@@ -1038,7 +1047,7 @@ size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
     const size_t npairs = (size_t)((B + 1) / 2), ck_floats = npairs * n_ckpt * 32 * (2 * nsl + 2);
     if ((int)npairs <= kDualMaxPairs)                            // + beta checkpoints and the emission-row layouts (ctc_dual.cu)
         return (dual_beta_offset(ck_floats, B) + ck_floats + npairs * 144 + 64) * 4;
-    return ck_floats * 4 + ((size_t)B + 2) * 16;                 // + one record per utterance
+    return (dual_beta_offset(ck_floats, B) + npairs * 144 + 64) * 4;   // + one record per utterance, one row layout per pair
 }
 #endif
 
