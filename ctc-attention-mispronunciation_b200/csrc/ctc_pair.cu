@@ -852,8 +852,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
         if (w < ((p.B + 1) >> 1)) ctc_pair_body<NSL, REGBUF, LOGITS, CH, false, PHASE>(p, ckpt_ws, n_ckpt, w, w, p.B);
         pdl_launch_dependents();
     } else {
-        pdl_launch_dependents();
-        pdl_wait();
+        pdl_wait();                                              // (the fp64 sweep behind this grid is released when it ends)
         // second tier: this warp owns checkpoint block w and walks the pairs w, w + #warps, ... of the flagged list
         const int n_utt = *p.list_count, stride = gridDim.x * (blockDim.x >> 5);
         if (n_utt <= p.list_team_max) return;                    // few flagged utterances: the team kernel has taken them

@@ -737,8 +737,7 @@ __global__ void __launch_bounds__(32 * (1 + NH), 2) ctc_team_kernel(CtcParams p,
         ctc_team_body<NSL, NH, LOGITS, CH, false>(p, ckpt_ws, n_ckpt, blockIdx.x, blockIdx.x, p.B, team_smem, true);
     } else {
         // the flagged utterances: this CTA owns checkpoint block blockIdx.x and walks the pairs blockIdx.x, + grid, ...
-        pdl_launch_dependents();
-        pdl_wait();
+        pdl_wait();                                              // (the next tier is released when this grid ends)
         const int n_utt = *p.list_count;
         if (n_utt > p.list_team_max) return;                     // many flagged utterances: the pair kernel's second tier takes them
         for (int pr = blockIdx.x; 2 * pr < n_utt; pr += gridDim.x)
