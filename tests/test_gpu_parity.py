@@ -111,6 +111,36 @@ def test_ctc_config3_slice_vs_torch_cpu(M, algo):
     _check_ctc(M, lp, tg, il, tl, algo=algo, max_fallback=0)
 
 
+@pytest.mark.parametrize("T,B,C,L", [(1, 1, 42, 1), (7, 3, 42, 3), (8, 2, 42, 4), (9, 5, 42, 4), (65, 33, 42, 20),
+                                     (200, 9, 43, 30), (333, 17, 42, 60), (1000, 40, 42, 120)])
+def test_ctc_few_utterances_concurrent_sweeps(M, T, B, C, L):
+    """The path of small batches (ctc_dual.cu + the segment instantiation of the backward kernel): alpha and beta are
+    swept concurrently with separate exponents, the gradient is computed on independent segments of every pair.  Shapes
+    around the chunk / segment boundaries, odd batch sizes (a pair with one half empty), ragged partners (one utterance
+    a fraction of the other's length), empty targets; every utterance against torch CPU fp64 (loss 1e-5 relative,
+    gradient 1e-4 absolute), nothing handed to the fp64 kernel, bitwise reproducible."""
+    from mddctc.loss import ctc_loss_raw
+    g = torch.Generator().manual_seed(100 + T + B)
+    lp = torch.log_softmax(torch.randn(T, B, C, generator=g), -1)
+    tg = torch.randint(1, C, (B, L), generator=g)
+    il = torch.randint(max(1, T // 4), T + 1, (B,), generator=g)
+    il[0] = T
+    tl = torch.minimum(torch.randint(0, L + 1, (B,), generator=g), (il - 1).clamp(min=0) // 2 + 1).clamp(max=L)
+    tl[0] = min(L, (T + 1) // 2)
+    if B > 2:
+        tl[2] = 0                                                 # an empty target next to a full one
+    _check_ctc(M, lp, tg, il, tl, algo=0, max_fallback=0)
+    a = ctc_loss_raw(lp.cuda(), tg.cuda(), il.cuda(), tl.cuda())
+    n0, g0 = a[0].clone(), a[1].clone()
+    b = ctc_loss_raw(lp.cuda(), tg.cuda(), il.cuda(), tl.cuda())
+    assert torch.equal(n0, b[0]) and torch.equal(g0, b[1])
+    # an infeasible utterance (more labels than frames allow) beside feasible ones: inf / NaN rows exactly as torch
+    if T >= 8 and B >= 2:
+        il2 = il.clone()
+        il2[1] = max(1, int(tl[1]) - 1) if int(tl[1]) > 1 else il2[1]
+        _check_ctc(M, lp, tg, il2, tl, algo=0)
+
+
 # ------------------------------------------------------------------------------- robustness envelope of the packed kernel
 def _aligned_logits(T, B, C, L, il, tl, tg, boost, noise, g):
     """Posteriors of a trained model: a random valid alignment of each target (labels on even frames, blanks between)
