@@ -88,6 +88,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "}\n" ::"r"(smem_u32(bar)), "r"(parity)
         : "memory");
 }
+// The same wait for a warp that is AHEAD of its partner (helpers waiting for a buffer to come free): the thread is
+// suspended by the hardware for up to `ns` at a time and woken by the phase completing, instead of polling -- a polling
+// warp takes issue slots from the warp it is waiting for when the two share a scheduler.
+__device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity, uint32_t ns = 4000) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAITI_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+        "@p bra DONEI_%=;\n"
+        "bra WAITI_%=;\n"
+        "DONEI_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity), "r"(ns)
+        : "memory");
+}
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(dst_smem)),

@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(64 * (1 + NH), 2) ctc_dual_kernel(CtcParams p,
             asm volatile("cp.async.wait_group 1;" ::: "memory");
             __syncwarp();
             if (k >= DNE) {                              // the lattice warp has left the buffer (chunk k - DNE of the sweep)
-                mbar_wait(&e_free[k % DNE], (ph_free >> (k % DNE)) & 1u);
+                mbar_wait_idle(&e_free[k % DNE], (ph_free >> (k % DNE)) & 1u);
                 ph_free ^= 1u << (k % DNE);
             }
             commit_rows(k);

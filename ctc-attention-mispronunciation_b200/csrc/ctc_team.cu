@@ -366,7 +366,7 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
             __syncwarp();
             TT(0)                                        // helper fwd: wait rows
             if (j >= TNE) {                              // the lattice warp has left the buffer (chunk j - TNE)
-                mbar_wait(&e_free[j % TNE], (ph_free >> (j % TNE)) & 1u);
+                mbar_wait_idle(&e_free[j % TNE], (ph_free >> (j % TNE)) & 1u);
                 ph_free ^= 1u << (j % TNE);
             }
             TT(1)                                        // helper fwd: wait e_free
@@ -395,7 +395,7 @@ __device__ __forceinline__ void ctc_team_body(const CtcParams& p, float* __restr
             const float g0 = kill0 ? 0.f : g[0], g1 = kill1 ? 0.f : g[1];
             const float og0 = g0 * (1.f / FIX), og1 = g1 * (1.f / FIX);
             TT(3)                                        // helper bwd: commit / issue
-            mbar_wait(&occ_full[nb & 1], (ph_occ >> (nb & 1)) & 1u);
+            mbar_wait_idle(&occ_full[nb & 1], (ph_occ >> (nb & 1)) & 1u);
             ph_occ ^= 1u << (nb & 1);
             TT(4)                                        // helper bwd: wait occ_full
             const float* Eb = E + (j % TNE) * (KF * RW);
