@@ -223,6 +223,7 @@ __global__ void __launch_bounds__(64 * (1 + NH), 2) ctc_dual_kernel(CtcParams p,
     if (!lattice_warp) {
         // ================================================================================================ helpers
         int oc[2][2], wp[4];
+        bool zs[4];                                      // my own position of (utterance, level) holds the zero item
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const unsigned free0 = __ballot_sync(FULL, ipos[h * 64 + lane] < 0), free1 = __ballot_sync(FULL, ipos[h * 64 + 32 + lane] < 0);
@@ -231,6 +232,7 @@ __global__ void __launch_bounds__(64 * (1 + NH), 2) ctc_dual_kernel(CtcParams p,
             for (int k = 0; k < 2; ++k) {
                 const int it = ipos[h * 64 + k * 32 + lane];     // class, C = the zero item, -1 = nobody
                 oc[h][k] = (it >= 0 && it < C) ? it : 0;
+                zs[2 * h + k] = it == C;
                 wp[2 * h + k] = h * CPMAX + (it == C ? fpos : k * 32 + lane);
             }
         }
@@ -246,6 +248,7 @@ __global__ void __launch_bounds__(64 * (1 + NH), 2) ctc_dual_kernel(CtcParams p,
         const float* ps0 = (ph0 ? lpb1 : lpb0) + 2 * (lane - ph0 * hC);
         const float* ps1 = (ph1 ? lpb1 : lpb0) + 2 * (lane + 32 - ph1 * hC);
         const unsigned raw_s = smem_u32(raw);
+        float* erow_pair = (want_grad && p.erow) ? p.erow + (size_t)pair * p.T * RW : nullptr;
         static_assert(CH % NH == 0, "a full chunk must split evenly over the helpers");
         const unsigned tstride_b = (unsigned)(p.stride_t * 4);   // row pitch in bytes (< 4 GB, checked by the launcher)
         auto issue_rows = [&](int k) {                   // my rows of this side's k-th chunk -> slot k % DNSLOT
@@ -315,6 +318,16 @@ __global__ void __launch_bounds__(64 * (1 + NH), 2) ctc_dual_kernel(CtcParams p,
                     d[wp[1]] = v0.y;
                     d[wp[2]] = v1.x;
                     d[wp[3]] = v1.y;
+                    // the beta side (its sweep has the lighter steps and ends first) also leaves the row, as it lies in
+                    // shared memory (position l + 32 k from lane l), to the segments of the second half: they neither
+                    // read the log-probs nor exponentiate them again
+                    if (side == 1 && erow_pair) {
+                        float* eg = erow_pair + (size_t)(t0 + r0 + kk * rs) * RW + lane;
+                        eg[0] = zs[0] ? 0.f : v0.x;
+                        eg[32] = zs[1] ? 0.f : v0.y;
+                        eg[64] = zs[2] ? 0.f : v1.x;
+                        eg[96] = zs[3] ? 0.f : v1.y;
+                    }
                 }
             };
             if (full) body(IC<CH / NH>{}, hid, NH);

@@ -68,17 +68,18 @@ __host__ __device__ constexpr int nslot(int phase) { return phase == 1 ? 2 : 3; 
 struct PairSmem {
     int occ_off, rows_off, abuf_off, ckst_off, raw_off, total_floats;
 };
-__host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf, int phase = 0) {
+__host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf, int phase = 0, bool seg = false) {
     PairSmem s;
     int o = 0;
     // class occupancies of the chunk, fixed point.  The setup tables (2*KF*RW ints) live in this block and the next;
     // the forward-only kernel has no occupancies: its tables lie over the emission rows and the staging slots.
     s.occ_off = o; if (phase != 1) o += KF * RW;
-    s.rows_off = o; o += KF * RW;                 // exp(lp) rows of the current chunk, both utterances
+    // exp(lp) rows of the current chunk, both utterances (segments: a ring of three chunks of the sweep kernel's rows)
+    s.rows_off = o; o += (seg ? nslot(phase) : 1) * KF * RW;
     s.abuf_off = o; if (!regbuf && phase != 1) o += KF * 32 * NSL;   // alpha label states of the chunk when they do not fit in registers
     s.ckst_off = o; if (phase != 1) o += 32 * (2 * NSL + 2);   // the next checkpoint, landing by cp.async (backward sweep)
     o = (o + 3) & ~3;
-    s.raw_off = o; o += nslot(phase) * KF * RAWW;  // log-prob rows as they arrive (class order); later the gradient rows
+    s.raw_off = o; if (!seg) o += nslot(phase) * KF * RAWW;  // log-prob rows as they arrive (class order)
     s.total_floats = (o + 3) & ~3;
     return s;
 }
@@ -99,6 +100,12 @@ template <int NSL, bool REGBUF, bool LOGITS, int CH, bool LIST, int PHASE = 0, b
 __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restrict__ ckpt_ws, int n_ckpt, int pair,
                                               int slot, int n_utt, int seg = 0) {
     static_assert(!SEG || (PHASE == 2 && !LIST), "segments: backward kernel of the first pass only");
+    // Segments do not read the log-probs at all: the sweep kernel's helpers have stored the exponentiated rows they
+    // committed, exactly as they lie in shared memory (512 B per pair-frame), and a segment lands them by cp.async where
+    // its lattice gathers them -- no second exponentiation, no second commit (13 of the backward sweep's 90 shared-
+    // memory wavefronts per pair-frame).  (At full batch size the extra 1 GB of writes makes the forward kernel
+    // DRAM-bound and the step no faster; a few hundred utterances are nowhere near that.)
+    constexpr bool ELOAD = SEG;
     using G = PGeo<NSL>;
     constexpr int NL = G::NL, ARS = G::ARS, CKW = G::CKW;
     static_assert(CH >= 1 && CH <= KF && (CH & (CH - 1)) == 0, "chunk length: a power of two up to the staged rows");
@@ -106,7 +113,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
 
     extern __shared__ __align__(16) float smem_f[];
     constexpr int NSLOT = nslot(PHASE);
-    const PairSmem lay = pair_smem_layout(NSL, REGBUF, PHASE);
+    const PairSmem lay = pair_smem_layout(NSL, REGBUF, PHASE, SEG);
     float* base = smem_f + (size_t)warp * lay.total_floats;
     unsigned* occ = reinterpret_cast<unsigned*>(base + lay.occ_off);   // [KF][RW], laid out like the emission rows
     float* rows = base + lay.rows_off;                           // [KF][RW]
@@ -364,7 +371,26 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     if constexpr (LOGITS) lsep = p.lse + ((lane & KF) ? bsrc1 : bsrc0);
     const unsigned raw_s = (unsigned)__cvta_generic_to_shared(raw);
     const unsigned tstride_b = (unsigned)(p.stride_t * 4);       // row pitch in bytes (< 4 GB, checked by the launcher)
+    const float* er = ELOAD ? p.erow + (size_t)slot * p.T * RW : nullptr;   // [T][RW] emission rows of this pair
+    const unsigned rows_s = (unsigned)__cvta_generic_to_shared(rows);
     auto issue_rows = [&](int j) {                       // rows of chunk j -> slot j % NSLOT (its own cp.async group)
+        if constexpr (ELOAD) {                           // 16 bytes per lane and frame, straight into the ring
+            if (j >= jlo && j < nch) {
+                int t0;
+                const bool full = chunk_geom(j, t0);
+                const unsigned d = rows_s + ((j % NSLOT) * (KF * RW) + lane * 4) * 4;
+                const float* q = er + (size_t)t0 * RW + lane * 4;
+                if (full) {
+#pragma unroll
+                    for (int r = 0; r < CH; ++r)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d + r * (RW * 4)), "l"(q + r * RW));
+                } else {
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(q));
+                }
+            }
+            asm volatile("cp.async.commit_group;");
+            return;
+        }
         if (j >= jlo && j < nch) {
             int t0;
             const bool full = chunk_geom(j, t0);
@@ -624,7 +650,9 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         asm volatile("cp.async.wait_group 1;" ::: "memory");
         __syncwarp();
         ckpt_take();
-        if (PHASE == 2 || j < nch - 1) commit_rows(nfc, j, kill0, kill1);   // (one kernel: the last chunk is still staged)
+        if constexpr (!ELOAD)
+            if (PHASE == 2 || j < nch - 1) commit_rows(nfc, j, kill0, kill1);   // (one kernel: the last chunk is still staged)
+        const int eo = ELOAD ? (j % NSLOT) * (KF * RW) : 0;     // where this chunk's emission rows lie
         __syncwarp();
         ckpt_issue(j - 1);                              // the staging block has been read
         // a / ea hold the checkpoint of this chunk: boundary factors and the beta exponents that go with it
@@ -670,7 +698,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
         float2 A[REGBUF ? NF : 1][NL];
 #pragma unroll
         for (int r = 0; r < NF; ++r) {
-            alpha_step<NSL>(a, sca, r * RW, bl0, bl1, ep0, ep1, ma);
+            alpha_step<NSL>(a, sca, eo + r * RW, bl0, bl1, ep0, ep1, ma);
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
                 if constexpr (REGBUF) A[r][q] = a[2 * q + 1];
@@ -688,7 +716,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
                 if constexpr (REGBUF) al[q] = A[r][q];
                 else al[q] = reinterpret_cast<const float2*>(abuf + r * ARS)[q * 32 + lane];
             }
-            beta_step<NSL>(bt, ul, scb, scb2, r * RW, bl0, bl1, ep0, ep1, mb);
+            beta_step<NSL>(bt, ul, scb, scb2, eo + r * RW, bl0, bl1, ep0, ep1, mb);
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
                 const float2 fx = __ffma2_rn(__fmul2_rn(al[q], ul[q]), zs2, magic2);
@@ -736,7 +764,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
 #pragma unroll
             for (int r = 0; r < NF; ++r) {
                 if (r + 1 < NF) cells(r + 1, on4, tn0, tn1);
-                const float* d = rows + r * RW;
+                const float* d = rows + eo + r * RW;
                 const float2 pv0 = make_float2(d[lane], d[32 + lane]), pv1 = make_float2(d[CPMAX + lane], d[CPMAX + 32 + lane]);
                 if (isb00) oc4[0] = fixi - ts0;
                 if (isb01) oc4[1] = fixi - ts0;
@@ -913,7 +941,7 @@ __global__ void __launch_bounds__(1024) compact_flagged_kernel(const int32_t* __
 
 template <int NSL, bool REGBUF, int MAXR, bool LOGITS, int CH, bool LIST, int PHASE = 0, bool SEG = false>
 int launch_cfg1(const CtcParams& p, float* ws, cudaStream_t st, int npairs) {
-    const PairSmem lay = pair_smem_layout(NSL, REGBUF, PHASE);
+    const PairSmem lay = pair_smem_layout(NSL, REGBUF, PHASE, SEG);
     size_t smem = (size_t)lay.total_floats * 4;                  // one warp (= one pair) per CTA
     // Warps per SM: the register file allows 8; fewer when that packs the pairs into full waves (a pair runs for the
     // whole kernel, so 13.8 pairs per SM are better served by 7 warps x 2 waves than by 8 + 5.8).
@@ -972,6 +1000,7 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
         float* ckb = ws + dual_beta_offset(ck_floats, p.B);
         p.ckb = ckb;
         p.cpos_ws = reinterpret_cast<int*>(ckb + ck_floats);
+        p.erow = ckb + ck_floats + (((size_t)npairs * 144 + 63) & ~(size_t)63);
         rc = launch_ctc_dual(p, ws, ckb, st, npairs);
         if (!rc) {
             const int want = nseg_env > 0 ? nseg_env : (7 * sm_count()) / npairs;     // one wave of 7 warps per SM
@@ -1045,7 +1074,7 @@ size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
     const size_t n_ckpt = (size_t)T / KF + 2 * KF;
     const size_t npairs = (size_t)((B + 1) / 2), ck_floats = npairs * n_ckpt * 32 * (2 * nsl + 2);
     if ((int)npairs <= kDualMaxPairs)                            // + beta checkpoints and the emission-row layouts (ctc_dual.cu)
-        return (dual_beta_offset(ck_floats, B) + ck_floats + npairs * 144 + 64) * 4;
+        return (dual_beta_offset(ck_floats, B) + ck_floats + npairs * 144 + 128 + npairs * (size_t)T * RW) * 4;   // + emission rows
     return (dual_beta_offset(ck_floats, B) + npairs * 144 + 64) * 4;   // + one record per utterance, one row layout per pair
 }
 #endif

@@ -44,6 +44,7 @@ struct CtcParams {
     float* ckb;
     int* cpos_ws;
     int nseg;
+    float* erow;              // [npairs][T][128] exponentiated emission rows as the sweep kernel committed them
     // loss sum folded into the fp64 kernel's launch: the first kernel of a call zeroes the ticket, the last CTA of the
     // fp64 sweep to finish adds up nll[B] in a fixed order (null: the caller launches sum_nll_kernel instead)
     unsigned* ticket;
