@@ -33,7 +33,7 @@ namespace {
 
 using namespace lattice;
 
-constexpr int DRAWW = 132;                 // floats per staged pair row: 2*C log-probs (C <= 63) + 2 row-LSE + pad
+constexpr int DRAWW = 132;                 // floats per staged pair row: 2*C log-probs (C <= 62) + 2 row-LSE + pad
 constexpr int DNSLOT = 3;                  // raw staging slots per side
 constexpr int DNE = 3;                     // emission buffers per side
 

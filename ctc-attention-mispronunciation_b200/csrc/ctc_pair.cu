@@ -61,7 +61,7 @@ namespace {
 
 using namespace lattice;
 
-constexpr int RAWW = 132;                  // floats per staged pair row: 2*C log-probs (C <= 63) + 2 row-LSE + pad (16 B multiple)
+constexpr int RAWW = 132;                  // floats per staged pair row: 2*C log-probs (C <= 62) + 2 row-LSE + pad (16 B multiple)
 // staging slots: the chunk being consumed and two in flight; the forward-only kernel (more warps per SM) keeps one in flight
 __host__ __device__ constexpr int nslot(int phase) { return phase == 1 ? 2 : 3; }
 
@@ -321,10 +321,6 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
     // the occupancy cells start at zero; zero pads of the staged rows (emission of unused label slots)
     if constexpr (PHASE != 1)
         for (int i = lane; i < KF * RW; i += 32) occ[i] = 0u;
-    if (lane < KF) {
-        rows[lane * RW + zslot0] = 0.f;
-        rows[lane * RW + zslot1] = 0.f;
-    }
     __syncwarp();
 
     // ------------------------------------------------------------------------------------------ geometry
@@ -448,6 +444,16 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
             wg[2 * h + k] = ov[h][k] ? h * C + oc[h][k] : 2 * C + 2;
         }
     }
+    // Only now, with the last of the set-up tables read: the emission of unused label slots.  (The tables lie over the
+    // emission rows; zeroing these slots before `ipos` had been read for the last time could turn the one free position
+    // of a 62-class row into an occupied one -- the zero item's owner then parked its store on a real class -- or hide
+    // the partner's zero item from its owner.  Found by the randomised sweep of round 2.)
+    __syncwarp();
+    if (lane < KF) {
+        rows[lane * RW + zslot0] = 0.f;
+        rows[lane * RW + zslot1] = 0.f;
+    }
+    __syncwarp();
     auto commit_rows = [&](auto nfc, int j, bool kill0, bool kill1) {   // p = exp(lp), bank-coloured; an idle half emits zeros
         constexpr int NF = decltype(nfc)::value;
         const float* slot = raw + (j % NSLOT) * (KF * RAWW);
@@ -1066,7 +1072,9 @@ int launch_nsl(const CtcParams& p, float* ws, cudaStream_t st) {
 }  // namespace
 
 #if !MDD_PAIR_TU_LOGITS
-bool ctc_pair_supported(int C, int Lmax) { return C <= 63 && pick_nsl(Lmax) != 0; }   // C classes + the zero item <= 64 slots
+// C classes + the zero item that unused label slots read + one free slot (where the lane that owns the zero item's
+// position parks its own store) must fit the 64 positions of an utterance's row
+bool ctc_pair_supported(int C, int Lmax) { return C <= 62 && pick_nsl(Lmax) != 0; }
 
 size_t ctc_pair_ws_bytes(int T, int B, int Lmax) {
     const int nsl = pick_nsl(Lmax);

@@ -27,7 +27,7 @@ namespace {
 
 using namespace lattice;
 
-constexpr int TRAWW = 132;                 // floats per staged pair row: 2*C log-probs (C <= 63) + 2 row-LSE + pad
+constexpr int TRAWW = 132;                 // floats per staged pair row: 2*C log-probs (C <= 62) + 2 row-LSE + pad
 constexpr int TNSLOT = 3;                  // raw staging slots (chunk % 3)
 constexpr int TNE = 3;                     // emission buffers (chunk % 3)
 
@@ -788,7 +788,7 @@ extern "C" void mdd_debug_team_cycles(unsigned long long* out, int reset) {
 }
 #endif
 
-bool ctc_team_supported(int C, int Lmax) { return C <= 63 && Lmax <= PGeo<8>::LCAP; }
+bool ctc_team_supported(int C, int Lmax) { return C <= 62 && Lmax <= PGeo<8>::LCAP; }   // (see ctc_pair_supported)
 
 // first pass over the whole batch (list == false) or second tier over the flagged list at 2 frames per chunk
 int launch_ctc_team(const CtcParams& p, void* ws, cudaStream_t st, bool list, int nblocks) {
