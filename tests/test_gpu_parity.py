@@ -176,6 +176,49 @@ def test_ctc_random_shapes_vs_fp64_kernel(M, seed):
     print("random shapes seed %d: worst loss rel %.2e, grad abs %.2e" % (seed, worst[0], worst[1]))
 
 
+@pytest.mark.parametrize("seed", [11, 12])
+def test_ctc_random_modes_vs_fp64_kernel(M, seed):
+    """The same sweep over the call's modes: logits in, concatenated 1-D targets, per-utterance upstream weights,
+    zero_infinity, peaky rows, long sequences (T up to 1300), long targets (L up to 255: every lattice width of the
+    packed path), class counts on both sides of its limit.  Loss within 1e-5 relative (+ 1e-6 absolute: a likelihood
+    within 1e-3 of 1 has a loss below fp32's resolution of P, in torch's fp32 path as much as here), gradient 1e-4,
+    identical inf / NaN pattern, bitwise reproducible."""
+    from mddctc.loss import ctc_loss_raw
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    ri = lambda lo, hi: int(torch.randint(lo, hi, (1,), generator=g, device="cuda"))
+    for it in range(90):
+        C = [5, 20, 42, 43, 62, 63, 64, 80][ri(0, 8)]
+        T = ri(1, 1300) if it % 5 == 0 else ri(1, 420)
+        B = ri(1, 40) if it % 3 == 0 else (ri(1, 600) if it % 3 == 1 else ri(600, 1300))
+        if T > 600:
+            B = min(B, 700)
+        L = ri(0, min([31, 63, 127, 255][ri(0, 4)], max(1, T // 2)) + 1)
+        mode = it % 6
+        x = torch.randn(T, B, C, generator=g, device="cuda") * [1.0, 1.0, 2.0, 0.3, 3.0][it % 5]
+        if mode == 4:                                             # peaky rows
+            x = x + 12.0 * torch.nn.functional.one_hot(torch.randint(0, C, (T, B), generator=g, device="cuda"), C)
+        logits = mode == 1
+        inp = x if logits else torch.log_softmax(x, -1)
+        il = torch.randint(1, T + 1, (B,), generator=g, device="cuda")
+        tl = torch.minimum(torch.randint(0, L + 1, (B,), generator=g, device="cuda"), (il + 1) // 2).clamp(max=L)
+        tg = torch.randint(1, C, (B, max(L, 1)), generator=g, device="cuda")
+        if mode == 3 and int(tl.sum()) > 0:                       # concatenated targets
+            tg = torch.cat([tg[b, :int(tl[b])] for b in range(B)])
+        go = torch.rand(B, generator=g, device="cuda") + 0.5 if mode == 5 else None
+        kw = dict(validate=False, zero_infinity=bool(it % 2), grad_out=go, logits=logits)
+        n0, g0, _ = ctc_loss_raw(inp, tg, il, tl, algo=0, **kw)
+        n0, g0 = n0.clone(), g0.clone()
+        n0b, g0b, _ = ctc_loss_raw(inp, tg, il, tl, algo=0, **kw)
+        assert torch.equal(n0, n0b) and torch.equal(g0.nan_to_num(7.0), g0b.nan_to_num(7.0)), (it, T, B, C, L, mode)
+        n1, g1, _ = ctc_loss_raw(inp, tg, il, tl, algo=1, **kw)
+        fin = torch.isfinite(n1)
+        assert torch.equal(torch.isfinite(n0), fin) and torch.equal(torch.isnan(g0), torch.isnan(g1)), (it, T, B, C, L, mode)
+        if bool(fin.any()):
+            assert bool(((n0[fin] - n1[fin]).abs() <= LOSS_RTOL * n1[fin].abs() + 1e-6).all()), (it, T, B, C, L, mode)
+            ok = ~torch.isnan(g1)
+            assert float((g0[ok] - g1[ok]).abs().max()) <= GRAD_ATOL, (it, T, B, C, L, mode)
+
+
 # ------------------------------------------------------------------------------- robustness envelope of the packed kernel
 def _aligned_logits(T, B, C, L, il, tl, tg, boost, noise, g):
     """Posteriors of a trained model: a random valid alignment of each target (labels on even frames, blanks between)
