@@ -61,7 +61,7 @@ __device__ unsigned long long g_dual_cycles[16];
 __device__ __forceinline__ void set_comp(float2& v, int h, float x) { if (h) v.y = x; else v.x = x; }
 
 template <int NSL, int NH, bool LOGITS>
-__global__ void __launch_bounds__(64 * (1 + NH), 2) ctc_dual_kernel(CtcParams p, float* __restrict__ ck_alpha,
+__global__ void __launch_bounds__(64 * (1 + NH), NH == 1 ? 4 : 2) ctc_dual_kernel(CtcParams p, float* __restrict__ ck_alpha,
                                                                     float* __restrict__ ck_beta, int n_ckpt) {
     using G = PGeo<NSL>;
     using LY = DualLayout<NSL, NH>;
@@ -558,9 +558,11 @@ int launch_dual1(const CtcParams& p, float* cka, float* ckb, cudaStream_t st, in
 
 template <int NSL, bool LOGITS>
 int launch_dual_nsl(const CtcParams& p, float* cka, float* ckb, cudaStream_t st, int npairs) {
-    // 4 helpers per side while every pair has an SM's worth of registers to itself, 2 when two or three CTAs share one
+    // 4 helpers per side while every pair has an SM's worth of registers to itself, 2 when two CTAs share one, 1 (four
+    // warps per CTA) when four do: the whole grid stays one wave up to four pairs per SM
     if (npairs <= sm_count()) return launch_dual1<NSL, 4, LOGITS>(p, cka, ckb, st, npairs);
-    return launch_dual1<NSL, 2, LOGITS>(p, cka, ckb, st, npairs);
+    if (npairs <= 2 * sm_count()) return launch_dual1<NSL, 2, LOGITS>(p, cka, ckb, st, npairs);
+    return launch_dual1<NSL, 1, LOGITS>(p, cka, ckb, st, npairs);
 }
 
 }  // namespace

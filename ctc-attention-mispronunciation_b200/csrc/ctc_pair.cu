@@ -898,7 +898,7 @@ ctc_pair_kernel(CtcParams p, float* __restrict__ ckpt_ws, int n_ckpt) {
     }
 }
 
-constexpr int kDualMaxPairs = 4 * kNumSM;                        // the concurrent-sweep path serves up to this many pairs
+constexpr int kDualMaxPairs = 4 * kNumSM;                        // the concurrent-sweep path serves up to this many pairs (four CTAs per SM)
 // floats from the start of the pair workspace to the beta checkpoints: alpha checkpoints, one record per utterance
 size_t dual_beta_offset(size_t ck_floats, int B) { return (ck_floats + ((size_t)B + 2) * 4 + 63) & ~(size_t)63; }
 
@@ -1000,7 +1000,9 @@ int launch_tiers(CtcParams p, float* ws, cudaStream_t st) {
     p.rec = reinterpret_cast<float4*>(ws + ck_floats);
     // Fewer still (and a gradient wanted): alpha and beta swept concurrently by ctc_dual.cu, then the backward kernel on
     // independent segments of every pair -- the dependent chain is T lattice steps instead of 3 T.
-    static int dual_max = std::min(env_int("MDD_CTC_DUAL_MAX_PAIRS", 2 * kNumSM), kDualMaxPairs);   // beyond: no faster (measured)
+    // (measured at T = 1000: 0.37 / 0.43 / 0.47 ms at 320 / 384 / 448 pairs against 0.47 / 0.48 / 0.50 for the kernels
+    // below; level at 512 pairs, slower beyond)
+    static int dual_max = std::min(env_int("MDD_CTC_DUAL_MAX_PAIRS", 3 * kNumSM), kDualMaxPairs);
     static int nseg_env = env_int("MDD_CTC_DUAL_NSEG", 0);
     if (team_ok && p.grad && npairs <= dual_max) {
         float* ckb = ws + dual_beta_offset(ck_floats, p.B);

@@ -73,7 +73,7 @@ void mdd_launch_count_reset(void);
  * loss_sum  : optional fp32 scalar out = sum_b nll[b] (deterministic fixed-order tree), e.g. an NCCL send buffer.
  * status    : optional int32[B].
  * algo      : 0 = auto: packed two-utterances-per-warp fp32 linear-domain kernel at 8 frames per chunk (for up to
- *                 296 pairs: alpha and beta swept concurrently, one CTA per pair, then the gradient on independent
+ *                 444 pairs: alpha and beta swept concurrently, one CTA per pair, then the gradient on independent
  *                 segments of every pair -- same arithmetic, a third of the dependent chain); the utterances
  *                 it flags (dynamic range, malformed rows) again at 2 frames per chunk; what is still flagged by the
  *                 fp64 linear-domain kernel (one CTA per utterance, exact to the rounding of the fp32 outputs),
