@@ -1,4 +1,4 @@
-// ctc_lattice.cuh -- lattice arithmetic shared by the linear-domain CTC kernels (ctc_pair.cu, ctc_duo.cu): geometry,
+// ctc_lattice.cuh -- lattice arithmetic shared by the linear-domain CTC kernels (ctc_pair.cu, ctc_team.cu, ctc_dual.cu): geometry,
 // packed alpha / beta steps for a pair of utterances, per-lane renormalisation.  See ctc_pair.cu for the scheme.
 #pragma once
 #include <type_traits>
@@ -129,7 +129,7 @@ __device__ __forceinline__ void beta_step(float2 (&b)[NSL], float2 (&ul)[NSL / 2
 // That is harmless for the leading edge of the lattice (states far ahead of the bulk carry paths of negligible mass)
 // and is checked after the fact where it is not: the backward sweep does not share the loss, so the total likelihood
 // it arrives at, beta_0(0) + beta_0(1), is compared with the forward P (flag 7 in ctc_pair.cu).  `strict` restores the
-// earlier a-priori criterion (any squash beyond 2^100 hands the utterance to the log-space kernel).
+// earlier a-priori criterion (any squash beyond 2^100 hands the utterance to the next tier).
 template <int NSL>
 __device__ __forceinline__ void renorm_alpha(float2 (&a)[NSL], int (&ea)[2], float2& sca, int lane, bool (&ok)[2],
                                              bool strict = false, int decay_max = 1 << 20) {

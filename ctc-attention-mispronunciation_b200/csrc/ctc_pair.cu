@@ -26,9 +26,9 @@
 //    integer atomic to the cell of its class, which sits at the class's (bank-coloured) emission position; the lane
 //    that owns the position reads it back.  Integer addition is associative: results are bitwise reproducible.
 //  * Nothing that travels far touches a register: log-prob rows go global -> shared by cp.async (8-byte pieces, two
-//    chunks ahead, three staging slots), checkpoints likewise one chunk ahead.  The gradient rows of a chunk are
-//    assembled in class order in the staging slot their log-probs came in and leave as 16-byte streaming stores
-//    when the pair's rows are contiguous and 16-byte aligned in the gradient array.
+//    chunks ahead, three staging slots), checkpoints likewise one chunk ahead.  Gradient values are stored straight
+//    from the lanes that own their classes (four 4-byte streaming stores per row; the sectors fill up in L2): staging
+//    the row in shared memory for wide stores costs more on the shared-memory pipe, which binds the kernel.
 //  * Dynamic range.  One exponent per lane and chunk is a finite window, and peaky posteriors move 20-35 bits per
 //    frame.  A renormalised lane keeps its maximum at 2^SHIFT; a lane far below its left neighbour is pulled up to
 //    2^-GAP of it and may lose its own content, which the backward sweep does not share: its total likelihood
@@ -38,8 +38,12 @@
 //    inside one chunk (flag 2).  DESIGN.md 5.1 has the measured envelope.
 //  * Three tiers.  Anything unusual (infeasible, empty, malformed, over/underflow, the guards above) sets flags[b].
 //    The flagged utterances are compacted into a list and run again by this same kernel at CH = 2 frames per chunk
-//    (LIST instantiation, persistent warps over the first pass's checkpoint blocks); ctc_log.cu then redoes whatever
-//    is still flagged in the same stream with torch's inf / NaN / zero_infinity semantics.
+//    (LIST instantiation, persistent warps over the first pass's checkpoint blocks; few flagged utterances go to the
+//    team kernel instead); the fp64 kernel of ctc_exact.cu then redoes whatever is still flagged in the same stream
+//    with torch's inf / NaN / zero_infinity semantics.
+//  * Two kernels per step (PHASE 1: forward sweep at 128 registers, PHASE 2: backward sweep), and for few utterances the
+//    backward sweep on independent segments of every pair (SEG) behind the concurrent alpha / beta sweeps of
+//    ctc_dual.cu.  Kernels that follow another kernel of the call are launched as programmatic dependents.
 //  * LOGITS instantiation: lp holds the output layer's logits, lse their row log-sum-exp (row_lse.cu); the emission
 //    is 2^(x log2 e - lse log2 e) and the gradient written is the one with respect to the logits.
 // This file is compiled twice so that the two halves of its instantiations build in parallel: as itself (log-prob
@@ -86,7 +90,7 @@ __host__ __device__ inline PairSmem pair_smem_layout(int NSL, bool regbuf, int p
 
 // CH = frames per chunk (renormalisation / checkpoint period): 8 for the first pass over the whole batch, 2 for the
 // second tier, which (LIST) walks the compacted list of the utterances the first pass flagged: four times the dynamic
-// range per frame for about twice the time per frame, in front of the log-space kernel.
+// range per frame for about twice the time per frame, in front of the fp64 kernel.
 // One pair of utterances, start to finish.  `pair` selects the utterances (2*pair, 2*pair+1 of the batch, or of the
 // compacted list), `slot` the checkpoint block of the workspace this warp may use.
 // PHASE 0: both sweeps in one kernel.  PHASE 1: the forward sweep alone (loss, checkpoints, a record of P per
@@ -155,7 +159,7 @@ __device__ __forceinline__ void ctc_pair_body(const CtcParams& p, float* __restr
                 bad = __any_sync(FULL, fl);
             }
             if (bad) {
-                if (lane == 0) p.flags[b] = 1;                   // the log-space kernel owns the error reporting
+                if (lane == 0) p.flags[b] = 1;                   // the fp64 kernel owns the error reporting
                 act[h] = false;
             } else {
                 Tb[h] = (int)Tb64;
