@@ -58,6 +58,23 @@ __device__ unsigned long long g_dual_cycles[16];
 #define DT(i)
 #endif
 
+// Non-blocking look at an mbarrier phase: issued at the top of a chunk, consumed after the renormalisation, so that the
+// ~100-cycle round trip of the wait that almost always succeeds (the helpers run up to three chunks ahead) is off the
+// lattice warp's dependent chain.
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
 __device__ __forceinline__ void set_comp(float2& v, int h, float x) { if (h) v.y = x; else v.x = x; }
 
 template <int NSL, int NH, bool LOGITS>
@@ -394,6 +411,7 @@ __global__ void __launch_bounds__(64 * (1 + NH), NH == 1 ? 4 : 2) ctc_dual_kerne
         auto fwd_chunk = [&](auto nfc, int j, int t0) {
             constexpr int NF = decltype(nfc)::value;
             const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
+            const bool ready = mbar_test(&e_full[j % DNE], (ph_full >> (j % DNE)) & 1u);
             {
                 bool ok[2];
                 renorm_alpha<NSL>(a, ea, sca, lane, ok, p.strict_squash != 0, p.decay_max);
@@ -407,7 +425,7 @@ __global__ void __launch_bounds__(64 * (1 + NH), NH == 1 ? 4 : 2) ctc_dual_kerne
                 reinterpret_cast<int2*>(c + 64 * NSL)[lane] = make_int2(ea[0], ea[1]);
             }
             const int eb = (j % DNE) * (KF * RW);
-            mbar_wait(&e_full[j % DNE], (ph_full >> (j % DNE)) & 1u);
+            if (!ready) mbar_wait(&e_full[j % DNE], (ph_full >> (j % DNE)) & 1u);
             ph_full ^= 1u << (j % DNE);
 #pragma unroll
             for (int r = 0; r < NF; ++r) alpha_step<NSL>(a, sca, eb + r * RW, bl0, bl1, ep0, ep1, mk);
@@ -475,6 +493,7 @@ __global__ void __launch_bounds__(64 * (1 + NH), NH == 1 ? 4 : 2) ctc_dual_kerne
             constexpr int NF = decltype(nfc)::value;
             const bool kill0 = !act[0] || t0 >= Tb[0], kill1 = !act[1] || t0 >= Tb[1];
             const int tend = t0 + NF;
+            const bool ready = mbar_test(&e_full[k % DNE], (ph_full >> (k % DNE)) & 1u);
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if (act[h] && tend == Tb[h]) {          // beta_T enters: 1 at the last state, nothing anywhere else
@@ -496,7 +515,7 @@ __global__ void __launch_bounds__(64 * (1 + NH), NH == 1 ? 4 : 2) ctc_dual_kerne
                 reinterpret_cast<int2*>(c + 64 * NSL)[lane] = make_int2(eb[0], eb[1]);
             }
             const int ebuf = (k % DNE) * (KF * RW);
-            mbar_wait(&e_full[k % DNE], (ph_full >> (k % DNE)) & 1u);
+            if (!ready) mbar_wait(&e_full[k % DNE], (ph_full >> (k % DNE)) & 1u);
             ph_full ^= 1u << (k % DNE);
 #pragma unroll
             for (int r = NF - 1; r >= 0; --r) {
