@@ -116,7 +116,8 @@ int mdd_ctc_loss_logits(const float* logits, int T, int B, int C, int64_t stride
  * cudaMalloc).  It calls no cudaMalloc / cudaFree and no allocating library routine; arguments, results and kernels are
  * those of mdd_ctc_loss.
  *   - Limit: shapes whose mdd_ctc_loss_workspace_bytes(T, B, C, max_target_len, algo) exceeds MDD_CTC_STATIC_WS_BYTES
- *     (16 MiB: e.g. B = 64 at T = 500, or B = 16 at T = 2000, with algo 0) are rejected with MDD_E_STATIC_LIMIT.
+ *     are rejected with MDD_E_STATIC_LIMIT.  16 MiB holds e.g. B = 64 at T = 500 with targets of up to 63 labels
+ *     (14.9 MiB with algo 0) or B = 16 at T = 2000 (14.0 MiB); B = 64 at T = 500 with 120 labels needs 20.8 MiB.
  *   - Every GPU that loads the library holds the 16 MiB until the process exits.
  *   - All calls on a device share the one array, which keeps the previous call's contents (the entry point clears the
  *     part that must start at zero on `stream`): calls that overlap on the GPU -- different streams, or threads --
